@@ -1,0 +1,617 @@
+// F1 / F2 -- logistic-regression optimiser kernels (SSGD, full-batch GD, MA, BMUF, EASGD).
+//
+// ref math: optimization/ssgd.py:23-33 (sigmoid, per-row gradient), :97-105 (sample, sum, update);
+//           machine_learning/logistic_regression.py:82-85 (sum, not mean);
+//           optimization/ma.py:39-43,96-106; optimization/bmuf.py:111-114;
+//           optimization/easgd.py:41-45,106.
+//
+// Two kernels:
+//  * lr_parity_kernel  -- the reference's default fp64 problem, the WHOLE training loop in one
+//    persistent cooperative launch (one CTA per logical Spark partition, in-kernel exchange).
+//  * lr_step_kernel    -- one optimiser step at benchmark scale (bf16/fp32 rows streamed once
+//    from HBM, forward + backward from the same registers, deterministic grid reduction, then the
+//    last CTA performs the cross-GPU all-reduce over peer memory and the optimiser update).
+#include <cooperative_groups.h>
+
+#include "comm.cuh"
+#include "philox.cuh"
+
+using namespace dapb;
+
+// =================================================================================================
+// Parity kernel
+// =================================================================================================
+namespace {
+
+__device__ __forceinline__ double reg_grad(double w, int reg_type, double a) {
+  // ref ssgd.py:36-47
+  if (reg_type == DAPB_REG_L2) return w;
+  double s = (w > 0.0) - (w < 0.0);
+  if (reg_type == DAPB_REG_L1) return s;
+  if (reg_type == DAPB_REG_ELASTIC) return a * s + (1.0 - a) * w;
+  return 0.0;
+}
+
+__global__ void __launch_bounds__(256) lr_parity_kernel(DapbLrParityArgs a, DapbComm c) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int D = a.D;
+  double* w = reinterpret_cast<double*>(smem_raw);   // global / centre weights (replicated)
+  double* wl = w + D;                                 // this partition's replica
+  double* contrib = wl + D;                           // what this partition contributes this round
+  double* dlt = contrib + D;                          // BMUF block momentum
+  double* rlist = dlt + D;                            // [max_part_rows] residuals of kept rows
+  int* idx = reinterpret_cast<int*>(rlist + a.max_part_rows);   // [max_part_rows] kept row ids
+  __shared__ int s_cnt, s_correct;
+
+  const int p_local = blockIdx.x;
+  const int gp = a.part_base + p_local;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = blockDim.x >> 5;
+  const int64_t r0 = a.part_off[p_local], r1 = a.part_off[p_local + 1];
+  const int n_p = (int)(r1 - r0);
+  const bool local_algo = a.algo >= DAPB_LR_MA;
+  const int stride = D + 1;                           // slot = D values + count
+
+  for (int d = tid; d < D; d += blockDim.x) {
+    w[d] = a.w[d];
+    wl[d] = a.ws ? a.ws[(int64_t)p_local * D + d] : a.w[d];
+    dlt[d] = a.delta_w ? a.delta_w[d] : 0.0;
+  }
+  __syncthreads();
+
+  for (int t = 0; t < a.T; ++t) {
+    // ---- 1. compact the kept rows of this partition, in row order (one warp) -----------------
+    if (wid == 0) {
+      int cnt = 0;
+      const uint8_t* m = a.masks ? a.masks + (int64_t)t * a.n_local + r0 : nullptr;
+      for (int base = 0; base < n_p; base += 32) {
+        int i = base + lane;
+        bool keep = i < n_p && (m == nullptr || m[i] != 0);
+        unsigned b = __ballot_sync(0xffffffffu, keep);
+        if (keep) idx[cnt + __popc(b & ((1u << lane) - 1))] = i;
+        cnt += __popc(b);
+      }
+      if (lane == 0) s_cnt = cnt;
+    }
+    __syncthreads();
+    const int cnt = s_cnt;
+
+    // ---- 2. local work ------------------------------------------------------------------------
+    if (local_algo && a.algo != DAPB_LR_EASGD)
+      for (int d = tid; d < D; d += blockDim.x) wl[d] = w[d];          // ref ma.py:96 reset
+    __syncthreads();
+    const int n_inner = local_algo ? (a.algo == DAPB_LR_EASGD ? 1 : a.n_local_iters) : 1;
+    for (int li = 0; li < n_inner; ++li) {
+      const double* wf = local_algo ? wl : w;
+      // residuals r_i = sigma(x_i . w) - y_i   (ref ssgd.py:33: -(y - f))
+      for (int k = wid; k < cnt; k += nw) {
+        const double* x = a.X + (r0 + idx[k]) * (int64_t)D;
+        double s = 0.0;
+        for (int d = lane; d < D; d += 32) s += x[d] * wf[d];
+        s = warp_sum(s);
+        if (lane == 0) rlist[k] = -(a.y[r0 + idx[k]] - sigmoid_ref(s, a.eps));
+      }
+      __syncthreads();
+      // ordered left fold over kept rows (Spark seqOp order), one thread per feature
+      for (int d = tid; d < D; d += blockDim.x) {
+        double g = 0.0;
+        for (int k = 0; k < cnt; ++k)
+          g = __dadd_rn(g, __dmul_rn(rlist[k], a.X[(r0 + idx[k]) * (int64_t)D + d]));
+        if (!local_algo) {
+          contrib[d] = g;
+        } else if (cnt > 0) {                  // empty sample: the reference raises (ma.py:41); we skip
+          double gm = g / (double)cnt;         // ref ma.py:42 np.mean
+          double nv = wl[d] - a.eta * gm;      // ref ma.py:43
+          if (a.algo == DAPB_LR_EASGD) nv -= a.alpha * (wl[d] - w[d]);   // ref easgd.py:45
+          contrib[d] = nv;                     // staged, committed to wl after the barrier
+        } else {
+          contrib[d] = wl[d];
+        }
+      }
+      __syncthreads();
+      if (local_algo) {
+        for (int d = tid; d < D; d += blockDim.x) wl[d] = contrib[d];
+        __syncthreads();
+      }
+    }
+
+    // ---- 3. exchange: push (contrib, cnt) to slot[gp] on every rank, partition-ordered sum ----
+    const uint64_t epoch = a.epoch_base + (uint64_t)t + 1;
+    const uint64_t par = (uint64_t)(epoch & 1) * a.P_global * stride;
+    for (int r = 0; r < c.world; ++r) {
+      double* slot = reinterpret_cast<double*>(comm_payload(c, r, a.payload_off)) + par + (uint64_t)gp * stride;
+      for (int d = tid; d < D; d += blockDim.x) slot[d] = contrib[d];
+      if (tid == 0) slot[D] = (double)cnt;
+    }
+    __syncthreads();
+    if (tid == 0) __threadfence_system();
+    __syncthreads();
+    if (tid < c.world) st_release_sys(comm_flags(c, tid) + a.flag_base + gp, epoch);
+    for (int q = tid; q < a.P_global; q += blockDim.x)
+      comm_wait_flag(comm_flags(c, c.rank) + a.flag_base + q, epoch);
+    __syncthreads();
+    const double* slots = reinterpret_cast<const double*>(comm_payload(c, c.rank, a.payload_off)) + par;
+    double cnt_tot = 0.0;
+    for (int q = 0; q < a.P_global; ++q) cnt_tot += __ldcg(slots + (uint64_t)q * stride + D);
+
+    // ---- 4. replicated update (identical on every CTA of every rank) --------------------------
+    for (int d = tid; d < D; d += blockDim.x) {
+      double S = __ldcg(slots + d);
+      for (int q = 1; q < a.P_global; ++q) S = __dadd_rn(S, __ldcg(slots + (uint64_t)q * stride + d));
+      double wd = w[d];
+      switch (a.algo) {
+        case DAPB_LR_SSGD:
+          if (cnt_tot > 0.0) wd -= a.eta * (S / cnt_tot + a.lam * reg_grad(wd, a.reg_type, a.reg_alpha));
+          break;                                                          // ref ssgd.py:105
+        case DAPB_LR_GD: wd -= a.eta * S; break;                          // ref logistic_regression.py:85
+        case DAPB_LR_MA: wd = S / (double)a.P_global; break;              // ref ma.py:106
+        case DAPB_LR_BMUF: {                                              // ref bmuf.py:111-114
+          double w_avg = S / (double)a.P_global;
+          double nd = a.mu * dlt[d] + a.zeta * (w_avg - wd);
+          dlt[d] = nd;
+          wd = wd + nd;
+        } break;
+        default:                                                          // ref easgd.py:106
+          wd = (1.0 - a.beta) * wd + a.beta * S / (double)a.P_global;
+      }
+      w[d] = wd;
+    }
+    __syncthreads();
+
+    // ---- 5. metrics by the CTA that owns global partition 0 (ref ssgd.py:107-112) -------------
+    if (gp == 0) {
+      if (tid == 0) s_correct = 0;
+      __syncthreads();
+      int ok = 0;
+      for (int i = wid; i < a.n_test; i += nw) {
+        const double* x = a.X_test + (int64_t)i * D;
+        double s = 0.0;
+        for (int d = lane; d < D; d += 32) s += x[d] * w[d];
+        s = warp_sum(s);
+        int pred = sigmoid_ref(s, a.eps) < 0.5 ? 0 : 1;
+        ok += (pred == a.y_test[i]);
+      }
+      if (lane == 0 && ok) atomicAdd(&s_correct, ok);
+      __syncthreads();
+      if (tid == 0) {
+        a.accs[t] = (double)s_correct / (double)a.n_test;
+        a.batch_sizes[t] = (int)cnt_tot;
+      }
+      if (a.w_hist)
+        for (int d = tid; d < D; d += blockDim.x) a.w_hist[(int64_t)t * D + d] = w[d];
+      __syncthreads();
+    }
+  }
+
+  for (int d = tid; d < D; d += blockDim.x) {
+    if (p_local == 0) {
+      a.w[d] = w[d];
+      if (a.delta_w) a.delta_w[d] = dlt[d];
+    }
+    if (a.ws) a.ws[(int64_t)p_local * D + d] = wl[d];
+  }
+}
+
+}  // namespace
+
+extern "C" uint64_t dapb_lr_parity_payload_bytes(int32_t P_global, int32_t D) {
+  return (uint64_t)2 * P_global * (D + 1) * sizeof(double);
+}
+
+extern "C" int dapb_lr_parity_run(const DapbLrParityArgs* args, const DapbComm* comm, void* stream) {
+  DAPB_REQUIRE(args && comm, "lr_parity_run: null argument");
+  DapbLrParityArgs a = *args;
+  DapbComm c = *comm;
+  DAPB_REQUIRE(c.world >= 1 && c.world <= DAPB_MAX_RANKS, "lr_parity_run: bad world %d", c.world);
+  DAPB_REQUIRE(a.P_local >= 1 && a.P_local <= dapb::sm_count(),
+               "lr_parity_run: P_local=%d must be in [1, #SM] (co-resident CTAs)", a.P_local);
+  DAPB_REQUIRE(a.P_global >= a.P_local && a.D >= 1 && a.T >= 0, "lr_parity_run: bad sizes");
+  DAPB_REQUIRE(a.algo >= DAPB_LR_SSGD && a.algo <= DAPB_LR_EASGD, "lr_parity_run: bad algo %d", a.algo);
+  uint64_t need = DAPB_FLAG_BYTES + a.payload_off + dapb_lr_parity_payload_bytes(a.P_global, a.D);
+  DAPB_REQUIRE(need <= c.heap_bytes, "lr_parity_run: heap too small (%llu > %llu)",
+               (unsigned long long)need, (unsigned long long)c.heap_bytes);
+  DAPB_REQUIRE((a.flag_base + a.P_global) * 8ull <= DAPB_FLAG_BYTES, "lr_parity_run: flag range");
+  size_t smem = (size_t)4 * a.D * sizeof(double) + (size_t)a.max_part_rows * (sizeof(double) + sizeof(int)) + 16;
+  DAPB_REQUIRE(smem <= 200 * 1024, "lr_parity_run: partition too large for the parity kernel (%zu B smem); "
+               "use dapb_lr_step for large data", smem);
+  DAPB_CUDA_CHECK(cudaFuncSetAttribute(lr_parity_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  void* kargs[] = {&a, &c};
+  DAPB_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)lr_parity_kernel, dim3(a.P_local), dim3(256), kargs, smem,
+                                              (cudaStream_t)stream));
+  return 0;
+}
+
+// =================================================================================================
+// Benchmark-scale step kernel
+// =================================================================================================
+namespace {
+
+constexpr int kStepThreads = 256;
+constexpr int kStepWarps = kStepThreads / 32;
+
+template <typename T> struct RowVec;   // 16-byte vector of T -> floats
+template <> struct RowVec<float> {
+  static constexpr int kElems = 4;
+  __device__ static __forceinline__ void unpack(const uint4& v, float* f) {
+    f[0] = __uint_as_float(v.x); f[1] = __uint_as_float(v.y);
+    f[2] = __uint_as_float(v.z); f[3] = __uint_as_float(v.w);
+  }
+};
+template <> struct RowVec<__nv_bfloat16> {
+  static constexpr int kElems = 8;
+  __device__ static __forceinline__ void unpack(const uint4& v, float* f) {
+    f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+    f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+  }
+};
+
+__device__ __forceinline__ float reg_grad_f(float w, int reg_type, float a) {
+  if (reg_type == DAPB_REG_L2) return w;
+  float s = (float)((w > 0.f) - (w < 0.f));
+  if (reg_type == DAPB_REG_L1) return s;
+  if (reg_type == DAPB_REG_ELASTIC) return a * s + (1.f - a) * w;
+  return 0.f;
+}
+
+// Finalize: executed by the LAST CTA of the grid once every CTA's partial is in `partials`.
+// g_s: shared scratch of >= D + 4 floats.
+__device__ void lr_finalize(const DapbLrStepArgs& a, const DapbComm& c, float* g_s) {
+  const int D = a.D, tid = threadIdx.x;
+  const int G = gridDim.x;
+  // deterministic sum over CTAs in blockIdx order
+  for (int d0 = tid * 4; d0 < D; d0 += blockDim.x * 4) {
+    if (d0 + 4 <= D && (D & 3) == 0) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+      for (int b = 0; b < G; ++b) {
+        float4 v = __ldcg(reinterpret_cast<const float4*>(a.partials + (int64_t)b * D + d0));
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      g_s[d0] = acc.x; g_s[d0 + 1] = acc.y; g_s[d0 + 2] = acc.z; g_s[d0 + 3] = acc.w;
+    } else {
+      for (int d = d0; d < min(d0 + 4, D); ++d) {
+        float acc = 0.f;
+        for (int b = 0; b < G; ++b) acc += __ldcg(a.partials + (int64_t)b * D + d);
+        g_s[d] = acc;
+      }
+    }
+  }
+  if (tid == 0) {
+    int cnt = 0;
+    for (int b = 0; b < G; ++b) cnt += __ldcg(a.counts + b);
+    g_s[D] = (float)cnt;          // exact for counts < 2^24; larger counts go through g_s[D+1..]
+    g_s[D + 1] = __int_as_float(cnt);
+  }
+  __syncthreads();
+  int cnt_local = __float_as_int(g_s[D + 1]);
+
+  if (a.fin == DAPB_LR_FIN_GRAD_ONLY) {
+    for (int d = tid; d < D; d += blockDim.x) a.g_out[d] = g_s[d];
+    if (tid == 0 && a.cnt_out) *a.cnt_out = cnt_local;
+    return;
+  }
+
+  if (a.fin == DAPB_LR_FIN_SSGD) {
+    // all-reduce [g | cnt(int bits in 2 halves)] : counts are summed exactly as two 16-bit halves in fp32
+    if (tid == 0) {
+      g_s[D] = (float)(cnt_local & 0xffff);
+      g_s[D + 1] = (float)(cnt_local >> 16);
+    }
+    __syncthreads();
+    block_allreduce_oneshot<float>(c, c.rank, a.payload_off, a.flag_base, a.epoch, g_s, g_s, D + 2);
+    const int cnt_i = (int)g_s[D] + ((int)g_s[D + 1] << 16);
+    const float cnt_tot = (float)cnt_i;
+    for (int d = tid; d < D; d += blockDim.x) {
+      float wd = a.w[d], g = g_s[d];
+      if (a.g_out) a.g_out[d] = g;
+      if (a.use_sum) wd -= a.eta * g;                                         // ref logistic_regression.py:85
+      else if (cnt_tot > 0.f) wd -= a.eta * (g / cnt_tot + a.lam * reg_grad_f(wd, a.reg_type, a.reg_alpha));
+      a.w[d] = wd;                                                            // ref ssgd.py:105
+    }
+    if (tid == 0 && a.cnt_out) *a.cnt_out = cnt_i;
+    return;
+  }
+
+  // LOCAL / LOCAL_SYNC : replica step  (ref ma.py:42-43, easgd.py:45)
+  for (int d = tid; d < D; d += blockDim.x) {
+    float wl = a.w_local[d];
+    if (cnt_local > 0) {
+      float nv = wl - a.eta * (g_s[d] / (float)cnt_local);
+      if (a.algo == DAPB_LR_EASGD) nv -= a.alpha * (wl - a.w[d]);
+      wl = nv;
+    }
+    g_s[d] = wl;
+    if (a.fin == DAPB_LR_FIN_LOCAL) a.w_local[d] = wl;
+  }
+  if (tid == 0 && a.cnt_out) *a.cnt_out = cnt_local;
+  if (a.fin == DAPB_LR_FIN_LOCAL) return;
+  __syncthreads();
+  // model all-reduce fused with the MA average / BMUF filter / EASGD centre update
+  // (ref ma.py:104-106, bmuf.py:109-114, easgd.py:104-106)
+  float* sum_s = g_s + ((D + 7) & ~3);
+  block_allreduce_oneshot<float>(c, c.rank, a.payload_off, a.flag_base, a.epoch, g_s, sum_s, D);
+  const float invP = 1.f / (float)a.n_replicas_total;
+  for (int d = tid; d < D; d += blockDim.x) {
+    float S = sum_s[d], wd = a.w[d];
+    if (a.algo == DAPB_LR_MA) wd = S * invP;
+    else if (a.algo == DAPB_LR_BMUF) {
+      float nd = a.mu * a.delta_w[d] + a.zeta * (S * invP - wd);
+      a.delta_w[d] = nd;
+      wd += nd;
+    } else wd = (1.f - a.beta) * wd + a.beta * S * invP;
+    a.w[d] = wd;
+    a.w_local[d] = a.reset_replica ? wd : g_s[d];
+  }
+}
+
+// Fast path: D == 32 * EPL (each lane owns EPL features, EPL/kElems 16-byte vectors per row).
+template <typename T, int EPL>
+__global__ void __launch_bounds__(kStepThreads, 2) lr_step_kernel(DapbLrStepArgs a, DapbComm c) {
+  constexpr int kE = RowVec<T>::kElems;
+  constexpr int kV = EPL / kE;                     // vectors per lane per row
+  constexpr int D = 32 * EPL;
+  extern __shared__ __align__(16) float smem[];   // [D (weights) | max(kStepWarps*D, 2*D+32)]
+  __shared__ int s_cnt;
+  __shared__ bool s_last;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+
+  // forward weights in shared memory, permuted to this kernel's lane order so that every lane
+  // reads its own float4s conflict-free: w4[(j*kQ + q)*32 + lane] = w[(j*32 + lane)*kE + 4q .. +4)
+  constexpr int kQ = kE / 4;
+  float4* w4 = reinterpret_cast<float4*>(smem);
+  float* red = smem + D;                               // [kStepWarps][D] reduction scratch
+  for (int i = tid; i < D / 4; i += kStepThreads) {
+    const int ln = i & 31, jq = i >> 5, j = jq / kQ, q = jq % kQ;
+    w4[i] = *reinterpret_cast<const float4*>(a.w_fwd + (j * 32 + ln) * kE + 4 * q);
+  }
+  float acc[EPL];
+#pragma unroll
+  for (int i = 0; i < EPL; ++i) acc[i] = 0.f;
+  int kept = 0;
+  if (tid == 0) s_cnt = 0;
+  __syncthreads();
+
+  const int64_t n_chunks = (a.n_rows + 31) >> 5;
+  const int64_t warp_g = (int64_t)blockIdx.x * kStepWarps + wid;
+  const int64_t warp_n = (int64_t)gridDim.x * kStepWarps;
+  const char* Xb = reinterpret_cast<const char*>(a.X);
+  const bool all_rows = a.mask == nullptr && a.threshold24 >= (1u << 24);
+
+  for (int64_t ch = warp_g; ch < n_chunks; ch += warp_n) {
+    const int64_t row = (ch << 5) + lane;
+    bool keep = row < a.n_rows;
+    if (keep && !all_rows)
+      keep = a.mask ? (a.mask[row] != 0)
+                    : philox_keep_row((uint64_t)(a.row_base + row), a.iteration, a.seed, a.threshold24);
+    unsigned bits = __ballot_sync(0xffffffffu, keep);
+    kept += __popc(bits);
+    while (bits) {
+      // two sampled rows in flight per warp (2 * kV independent 16-byte loads per lane)
+      const int b0 = __ffs(bits) - 1; bits &= bits - 1;
+      const int b1 = bits ? __ffs(bits) - 1 : -1; if (b1 >= 0) bits &= bits - 1;
+      const int64_t ra = (ch << 5) + b0, rb = (ch << 5) + (b1 >= 0 ? b1 : b0);
+      uint4 va[kV], vb[kV];
+      const char* pa = Xb + ra * (int64_t)(D * sizeof(T));
+      const char* pb = Xb + rb * (int64_t)(D * sizeof(T));
+#pragma unroll
+      for (int j = 0; j < kV; ++j) va[j] = ld_stream_16(pa + (size_t)(j * 32 + lane) * 16);
+#pragma unroll
+      for (int j = 0; j < kV; ++j) vb[j] = ld_stream_16(pb + (size_t)(j * 32 + lane) * 16);
+      const float ya = a.y[ra], yb = a.y[rb];
+      float xa[EPL], dota = 0.f;
+#pragma unroll
+      for (int j = 0; j < kV; ++j) RowVec<T>::unpack(va[j], xa + j * kE);
+      float dotb = 0.f;
+#pragma unroll
+      for (int j = 0; j < kV; ++j) {
+        float xb[kE], wv[kE];
+        RowVec<T>::unpack(vb[j], xb);
+#pragma unroll
+        for (int q = 0; q < kQ; ++q) {
+          const float4 t4 = w4[(j * kQ + q) * 32 + lane];
+          wv[4 * q] = t4.x; wv[4 * q + 1] = t4.y; wv[4 * q + 2] = t4.z; wv[4 * q + 3] = t4.w;
+        }
+#pragma unroll
+        for (int e = 0; e < kE; ++e) {
+          dota = fmaf(xa[j * kE + e], wv[e], dota);
+          dotb = fmaf(xb[e], wv[e], dotb);
+        }
+      }
+      dota = warp_sum(dota);
+      dotb = warp_sum(dotb);
+      const float resa = sigmoid_ref(dota, a.eps) - ya;                    // ref ssgd.py:33
+      const float resb = b1 >= 0 ? sigmoid_ref(dotb, a.eps) - yb : 0.f;
+#pragma unroll
+      for (int i = 0; i < EPL; ++i) acc[i] = fmaf(resa, xa[i], acc[i]);
+#pragma unroll
+      for (int j = 0; j < kV; ++j) {
+        float xb[kE];
+        RowVec<T>::unpack(vb[j], xb);
+#pragma unroll
+        for (int e = 0; e < kE; ++e) acc[j * kE + e] = fmaf(resb, xb[e], acc[j * kE + e]);
+      }
+    }
+  }
+
+  // ---- CTA reduction: warps -> smem -> one partial row per CTA --------------------------------
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < kV; ++j)
+#pragma unroll
+    for (int e = 0; e < kE; ++e) red[wid * D + (j * 32 + lane) * kE + e] = acc[j * kE + e];
+  if (lane == 0 && kept) atomicAdd(&s_cnt, kept);
+  __syncthreads();
+  for (int d = tid; d < D; d += kStepThreads) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < kStepWarps; ++w) s += red[w * D + d];
+    a.partials[(int64_t)blockIdx.x * D + d] = s;
+  }
+  if (tid == 0) a.counts[blockIdx.x] = s_cnt;
+  // ---- last-CTA election -------------------------------------------------------------------------
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    unsigned t = atomicAdd(a.ticket, 1u);
+    s_last = (t == gridDim.x - 1);
+    if (s_last) *a.ticket = 0;                         // ready for the next launch
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  lr_finalize(a, c, red);
+}
+
+// Generic path (any D <= 8192): per-warp accumulators in shared memory.
+template <typename T>
+__global__ void __launch_bounds__(kStepThreads) lr_step_generic_kernel(DapbLrStepArgs a, DapbComm c) {
+  extern __shared__ __align__(16) float smem[];       // [kStepWarps][D] (+ finalize scratch)
+  __shared__ int s_cnt;
+  __shared__ bool s_last;
+  const int D = a.D, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  float* acc = smem + (int64_t)wid * D;
+  for (int d = lane; d < D; d += 32) acc[d] = 0.f;
+  if (tid == 0) s_cnt = 0;
+  __syncthreads();
+  int kept = 0;
+  const T* X = reinterpret_cast<const T*>(a.X);
+  const int64_t warp_g = (int64_t)blockIdx.x * kStepWarps + wid, warp_n = (int64_t)gridDim.x * kStepWarps;
+  const bool all_rows = a.mask == nullptr && a.threshold24 >= (1u << 24);
+  for (int64_t row = warp_g; row < a.n_rows; row += warp_n) {
+    bool keep = all_rows ? true
+                : a.mask ? (a.mask[row] != 0)
+                         : philox_keep_row((uint64_t)(a.row_base + row), a.iteration, a.seed, a.threshold24);
+    if (!keep) continue;
+    ++kept;
+    const T* x = X + row * (int64_t)D;
+    float s = 0.f;
+    for (int d = lane; d < D; d += 32) s = fmaf((float)x[d], a.w_fwd[d], s);
+    s = warp_sum(s);
+    const float r = sigmoid_ref(s, a.eps) - a.y[row];
+    for (int d = lane; d < D; d += 32) acc[d] = fmaf(r, (float)x[d], acc[d]);
+  }
+  if (lane == 0 && kept) atomicAdd(&s_cnt, kept);
+  __syncthreads();
+  for (int d = tid; d < D; d += kStepThreads) {
+    float s = 0.f;
+    for (int w = 0; w < kStepWarps; ++w) s += smem[(int64_t)w * D + d];
+    a.partials[(int64_t)blockIdx.x * D + d] = s;
+  }
+  if (tid == 0) a.counts[blockIdx.x] = s_cnt;
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    unsigned t = atomicAdd(a.ticket, 1u);
+    s_last = (t == gridDim.x - 1);
+    if (s_last) *a.ticket = 0;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  lr_finalize(a, c, smem);
+}
+
+template <typename T, int EPL>
+int launch_fast(const DapbLrStepArgs& a, const DapbComm& c, int grid, cudaStream_t s) {
+  constexpr int D = 32 * EPL;
+  size_t smem = sizeof(float) * (size_t)(D + (kStepWarps * D > 2 * D + 32 ? kStepWarps * D : 2 * D + 32));
+  DAPB_CUDA_CHECK(cudaFuncSetAttribute(lr_step_kernel<T, EPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  lr_step_kernel<T, EPL><<<grid, kStepThreads, smem, s>>>(a, c);
+  DAPB_LAUNCH_CHECK();
+  return 0;
+}
+template <typename T>
+int launch_generic(const DapbLrStepArgs& a, const DapbComm& c, int grid, cudaStream_t s) {
+  size_t smem = sizeof(float) * (size_t)(kStepWarps * a.D > 2 * a.D + 32 ? kStepWarps * a.D : 2 * a.D + 32);
+  DAPB_REQUIRE(smem <= 220 * 1024, "lr_step: D=%d too large for the generic kernel", a.D);
+  DAPB_CUDA_CHECK(cudaFuncSetAttribute(lr_step_generic_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  lr_step_generic_kernel<T><<<grid, kStepThreads, smem, s>>>(a, c);
+  DAPB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int dapb_lr_step(const DapbLrStepArgs* args, const DapbComm* comm, void* stream) {
+  DAPB_REQUIRE(args && comm, "lr_step: null argument");
+  DapbLrStepArgs a = *args;
+  DapbComm c = *comm;
+  DAPB_REQUIRE(a.dtype == 0 || a.dtype == 1, "lr_step: dtype must be 0 (fp32) or 1 (bf16)");
+  DAPB_REQUIRE(a.D >= 1 && a.n_rows >= 0, "lr_step: bad shape");
+  DAPB_REQUIRE(a.fin >= DAPB_LR_FIN_GRAD_ONLY && a.fin <= DAPB_LR_FIN_LOCAL_SYNC, "lr_step: bad fin");
+  DAPB_REQUIRE(a.partials && a.counts && a.ticket && a.w_fwd, "lr_step: missing scratch / weights");
+  if (a.fin == DAPB_LR_FIN_SSGD || a.fin == DAPB_LR_FIN_LOCAL_SYNC) {
+    DAPB_REQUIRE(c.world >= 1 && c.world <= DAPB_MAX_RANKS, "lr_step: bad world");
+    DAPB_REQUIRE(a.epoch >= 1, "lr_step: epoch starts at 1");
+    if (c.world > 1) {
+      uint64_t need = DAPB_FLAG_BYTES + a.payload_off + (uint64_t)2 * c.world * ((a.D + 2 + 3) & ~3) * sizeof(float);
+      DAPB_REQUIRE(need <= c.heap_bytes, "lr_step: heap too small");
+    }
+  }
+  int grid = a.grid > 0 ? a.grid : 2 * dapb::sm_count();
+  a.grid = grid;
+  cudaStream_t s = (cudaStream_t)stream;
+  const bool aligned = (reinterpret_cast<uintptr_t>(a.X) & 15) == 0;
+  if (aligned && a.dtype == 1) {
+    switch (a.D) {
+      case 256: return launch_fast<__nv_bfloat16, 8>(a, c, grid, s);
+      case 512: return launch_fast<__nv_bfloat16, 16>(a, c, grid, s);
+      case 1024: return launch_fast<__nv_bfloat16, 32>(a, c, grid, s);
+      default: break;
+    }
+  } else if (aligned && a.dtype == 0) {
+    switch (a.D) {
+      case 128: return launch_fast<float, 4>(a, c, grid, s);
+      case 256: return launch_fast<float, 8>(a, c, grid, s);
+      case 512: return launch_fast<float, 16>(a, c, grid, s);
+      case 1024: return launch_fast<float, 32>(a, c, grid, s);
+      default: break;
+    }
+  }
+  return a.dtype == 1 ? launch_generic<__nv_bfloat16>(a, c, grid, s) : launch_generic<float>(a, c, grid, s);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Accuracy (ref ssgd.py:107-110): pred = sigmoid(x.w) < 0.5 ? 0 : 1; acc = mean(pred == y)
+// ---------------------------------------------------------------------------------------------
+namespace {
+template <typename T>
+__global__ void lr_eval_kernel(const T* X, const float* y, int64_t n, int D, const float* w, float eps,
+                               float* acc_out, uint32_t* scratch) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp_g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t warp_n = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  unsigned ok = 0;
+  for (int64_t row = warp_g; row < n; row += warp_n) {
+    const T* x = X + row * (int64_t)D;
+    float s = 0.f;
+    for (int d = lane; d < D; d += 32) s = fmaf((float)x[d], w[d], s);
+    s = warp_sum(s);
+    float pred = sigmoid_ref(s, eps) < 0.5f ? 0.f : 1.f;
+    ok += (pred == y[row]);
+  }
+  if (lane == 0 && ok) atomicAdd(&scratch[0], ok);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned t = atomicAdd(&scratch[1], 1u);
+    if (t == gridDim.x - 1) {
+      __threadfence();
+      *acc_out = (float)((double)atomicAdd(&scratch[0], 0u) / (double)n);
+      scratch[0] = 0; scratch[1] = 0;
+    }
+  }
+}
+}  // namespace
+
+extern "C" int dapb_lr_eval(const void* X, const float* y, int64_t n_rows, int32_t D, int32_t dtype,
+                            const float* w, float eps, float* acc_out, uint32_t* scratch2, void* stream) {
+  DAPB_REQUIRE(n_rows > 0 && D > 0 && scratch2 && acc_out, "lr_eval: bad arguments");
+  int grid = (int)((n_rows * 32 + 255) / 256);
+  if (grid > 4 * dapb::sm_count()) grid = 4 * dapb::sm_count();
+  if (dtype == 1)
+    lr_eval_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)X, y, n_rows, D, w, eps, acc_out, scratch2);
+  else
+    lr_eval_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)X, y, n_rows, D, w, eps, acc_out, scratch2);
+  DAPB_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,154 @@
+"""ctypes binding of ``_lib/libdapb200.so`` (C ABI in ``include/dapb200.h``).
+
+The library is loaded lazily.  On a machine with a GPU a missing or unloadable library is an error
+(the CUDA path must be the one that runs -- no silent eager fallback); on a CPU-only machine
+``available()`` is False and the torch/NumPy backends are used instead.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+from . import build as _build
+
+MAX_RANKS = 8
+FLAG_BYTES = 65536
+
+_lib: Optional[C.CDLL] = None
+_load_error: Optional[str] = None
+
+
+class DapbComm(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32),
+                ("heap", C.c_void_p * MAX_RANKS), ("heap_bytes", C.c_uint64)]
+
+
+class DapbLrParityArgs(C.Structure):
+    _fields_ = [
+        ("X", C.c_void_p), ("y", C.c_void_p), ("part_off", C.c_void_p), ("masks", C.c_void_p),
+        ("X_test", C.c_void_p), ("y_test", C.c_void_p),
+        ("n_local", C.c_int64),
+        ("n_test", C.c_int32), ("D", C.c_int32), ("P_local", C.c_int32), ("P_global", C.c_int32),
+        ("part_base", C.c_int32), ("T", C.c_int32),
+        ("algo", C.c_int32), ("n_local_iters", C.c_int32), ("reg_type", C.c_int32), ("max_part_rows", C.c_int32),
+        ("eta", C.c_double), ("lam", C.c_double), ("reg_alpha", C.c_double), ("mu", C.c_double),
+        ("zeta", C.c_double), ("alpha", C.c_double), ("beta", C.c_double), ("eps", C.c_double),
+        ("w", C.c_void_p), ("ws", C.c_void_p), ("delta_w", C.c_void_p), ("accs", C.c_void_p),
+        ("batch_sizes", C.c_void_p), ("w_hist", C.c_void_p),
+        ("payload_off", C.c_uint64), ("flag_base", C.c_uint32), ("epoch_base", C.c_uint64),
+    ]
+
+
+class DapbLrStepArgs(C.Structure):
+    _fields_ = [
+        ("X", C.c_void_p), ("y", C.c_void_p), ("n_rows", C.c_int64), ("row_base", C.c_int64),
+        ("D", C.c_int32), ("dtype", C.c_int32),
+        ("mask", C.c_void_p), ("seed", C.c_uint64), ("iteration", C.c_uint32), ("threshold24", C.c_uint32),
+        ("eps", C.c_float), ("w_fwd", C.c_void_p),
+        ("partials", C.c_void_p), ("counts", C.c_void_p), ("ticket", C.c_void_p), ("grid", C.c_int32),
+        ("fin", C.c_int32), ("algo", C.c_int32), ("reg_type", C.c_int32), ("use_sum", C.c_int32),
+        ("eta", C.c_float), ("lam", C.c_float), ("reg_alpha", C.c_float), ("mu", C.c_float),
+        ("zeta", C.c_float), ("alpha", C.c_float), ("beta", C.c_float),
+        ("n_replicas_total", C.c_int32),
+        ("g_out", C.c_void_p), ("cnt_out", C.c_void_p), ("w", C.c_void_p), ("w_local", C.c_void_p),
+        ("delta_w", C.c_void_p), ("reset_replica", C.c_int32),
+        ("payload_off", C.c_uint64), ("flag_base", C.c_uint32), ("epoch", C.c_uint64),
+    ]
+
+
+ALGO_ID = {"ssgd": 0, "gd": 1, "ma": 2, "bmuf": 3, "easgd": 4}
+REG_ID = {"none": 0, "l2": 1, "l1": 2, "elastic_net": 3}
+FIN_GRAD_ONLY, FIN_SSGD, FIN_LOCAL, FIN_LOCAL_SYNC = 0, 1, 2, 3
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def _declare(lib: C.CDLL):
+    vp, i32, i64, u32, u64 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_uint64
+    f32, f64 = C.c_float, C.c_double
+    P = C.POINTER
+    sig = {
+        "dapb_last_error": (C.c_char_p, []),
+        "dapb_version": (C.c_int, []),
+        "dapb_device_info": (C.c_int, [P(i32), P(i32), P(i32), P(u64)]),
+        "dapb_symm_alloc": (C.c_int, [u64, P(vp)]),
+        "dapb_symm_free": (C.c_int, [vp]),
+        "dapb_ipc_get_handle": (C.c_int, [vp, vp]),
+        "dapb_ipc_open_handle": (C.c_int, [vp, P(vp)]),
+        "dapb_ipc_close_handle": (C.c_int, [vp]),
+        "dapb_comm_selftest": (C.c_int, [vp, u64, i32, i32, i32, vp, vp]),
+        "dapb_allreduce_f32": (C.c_int, [P(DapbComm), u64, u32, u64, vp, vp, i32, vp]),
+        "dapb_allreduce_f64": (C.c_int, [P(DapbComm), u64, u32, u64, vp, vp, i32, vp]),
+        "dapb_barrier": (C.c_int, [P(DapbComm), u32, u64, vp]),
+        "dapb_lr_parity_run": (C.c_int, [P(DapbLrParityArgs), P(DapbComm), vp]),
+        "dapb_lr_parity_payload_bytes": (u64, [i32, i32]),
+        "dapb_lr_step": (C.c_int, [P(DapbLrStepArgs), P(DapbComm), vp]),
+        "dapb_lr_eval": (C.c_int, [vp, vp, i64, i32, i32, vp, f32, vp, vp, vp]),
+        "dapb_mc_pi": (C.c_int, [u64, u64, u64, vp, vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name, None)
+        if fn is None:
+            continue
+        fn.restype = res
+        fn.argtypes = args
+
+
+def load(build_if_missing: bool = True) -> C.CDLL:
+    global _lib, _load_error
+    if _lib is not None:
+        return _lib
+    path = _build.LIB_PATH
+    if not path.exists() and build_if_missing:
+        _build.build()
+    try:
+        _lib = C.CDLL(str(path), mode=C.RTLD_GLOBAL)
+    except OSError as e:                                           # pragma: no cover
+        _load_error = str(e)
+        raise NativeError(f"cannot load {path}: {e}") from e
+    _declare(_lib)
+    return _lib
+
+
+def cuda_available() -> bool:
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:                                              # pragma: no cover
+        return False
+
+
+def available() -> bool:
+    """True iff the native CUDA path can run here (GPU present and library loadable).
+    On a GPU machine a load failure raises instead of returning False."""
+    if not cuda_available():
+        return False
+    load()
+    return True
+
+
+def check(rc: int, what: str = ""):
+    if rc != 0:
+        msg = load().dapb_last_error().decode("utf-8", "replace")
+        raise NativeError(f"{what or 'dapb call'} failed (rc={rc}): {msg}")
+
+
+def ptr(t) -> int:
+    """Device/host pointer of a torch tensor (0 for None)."""
+    return 0 if t is None else t.data_ptr()
+
+
+def stream_ptr(stream=None) -> int:
+    import torch
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return s.cuda_stream
+
+
+def local_comm(heap_ptr: int, heap_bytes: int) -> DapbComm:
+    c = DapbComm()
+    c.rank, c.world, c.heap_bytes = 0, 1, heap_bytes
+    c.heap[0] = heap_ptr
+    return c

@@ -1,0 +1,382 @@
+"""Logistic regression trained by SSGD / full-batch GD / Model Averaging / BMUF / EASGD.
+
+Reference drivers: ``optimization/ssgd.py:93-112``, ``machine_learning/logistic_regression.py:76-92``,
+``optimization/ma.py:93-113``, ``optimization/bmuf.py:98-121``, ``optimization/easgd.py:95-113``.
+
+Three interchangeable backends produce a :class:`LogisticResult`:
+
+``oracle``  NumPy restatement with exact Spark semantics (``oracle.algorithms.logistic_oracle``).
+``torch``   plain PyTorch + ``torch.distributed`` (NCCL on GPUs, gloo on CPU) -- the in-box baseline.
+``fused``   the sm_100a kernels of ``csrc/lr.cu``: for the reference's small fp64 problem the whole
+            training loop is one persistent kernel; at benchmark scale each step is one launch that
+            fuses sampling, forward, backward, grid reduction, the cross-GPU all-reduce over peer
+            memory and the optimiser update (:class:`ShardedLogisticEngine`).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional
+
+import numpy as np
+import torch
+
+from .. import _native
+from ..config import LogisticConfig
+from ..data.datasets import LogisticData
+from ..oracle import spark_semantics as sp
+from ..oracle.algorithms import LogisticInit, LogisticResult, logistic_oracle
+from ..parallel.dist import Dist, current
+from ..parallel.partition import RowSharding
+from ..utils.philox import bernoulli_threshold, philox_row_mask_np, philox_row_mask_torch
+
+
+# ------------------------------------------------------------------------------------------------
+def sample_masks(cfg: LogisticConfig, sizes: np.ndarray, n_iterations: Optional[int] = None) -> Optional[np.ndarray]:
+    """Keep-masks [T, N] (uint8) for every iteration, or None for full-batch GD.
+    ``spark``: MT19937 stream of ``rdd.sample(False, f, 42 + t)`` (ssgd.py:97); ``philox``: device sampler."""
+    T = cfg.n_iterations if n_iterations is None else n_iterations
+    if cfg.algo == "gd":
+        return None
+    n = int(np.sum(sizes))
+    if cfg.sampler == "spark":
+        return sp.bernoulli_sample_masks(sizes, cfg.mini_batch_fraction, cfg.sample_seed, T).astype(np.uint8)
+    return np.stack([philox_row_mask_np(n, cfg.mini_batch_fraction, cfg.sample_seed, t) for t in range(T)]).astype(np.uint8)
+
+
+def _resolve_backend(backend: str) -> str:
+    if backend != "auto":
+        return backend
+    return "fused" if _native.available() else "torch"
+
+
+def run_logistic(data: LogisticData, cfg: LogisticConfig, init: Optional[LogisticInit] = None,
+                 backend: str = "auto", dist: Optional[Dist] = None,
+                 masks: Optional[np.ndarray] = None, record_w: bool = False) -> LogisticResult:
+    """Train on ``data`` exactly as the reference script for ``cfg.algo`` does."""
+    backend = _resolve_backend(backend)
+    if init is None:
+        init = LogisticInit.draw(cfg.algo, data.dim, cfg.n_slices, cfg.seed)
+    if backend == "oracle":
+        return logistic_oracle(data.matrix, data.X_test_aug, data.y_test, cfg, init,
+                               masks=None if masks is None else masks.astype(bool))
+    dist = dist or current()
+    sh = RowSharding.spark(data.matrix.shape[0], cfg.n_slices, dist.world)
+    if masks is None:
+        masks = sample_masks(cfg, sh.sizes())
+    if backend == "torch":
+        return _run_torch(data, cfg, init, dist, sh, masks)
+    if backend == "fused":
+        return _run_fused_parity(data, cfg, init, dist, sh, masks, record_w)
+    raise ValueError(f"unknown backend {backend!r}")
+
+
+# ------------------------------------------------------------------------------------------------ torch baseline
+def _sigmoid(z: torch.Tensor, eps: float) -> torch.Tensor:
+    return 1.0 / (torch.exp(-z) + 1.0 + eps)
+
+
+def _run_torch(data, cfg, init, dist, sh, masks) -> LogisticResult:
+    dev, f64 = dist.device, torch.float64
+    parts = sh.local_partitions(dist.rank)
+    r0, r1 = sh.local_row_range(dist.rank)
+    X = torch.as_tensor(data.X_aug[r0:r1], dtype=f64, device=dev)
+    y = torch.as_tensor(data.y[r0:r1], dtype=f64, device=dev)
+    loc = sh.local_offsets(dist.rank)
+    Xt = torch.as_tensor(data.X_test_aug, dtype=f64, device=dev)
+    yt = torch.as_tensor(data.y_test, dtype=torch.int64, device=dev)
+    m = None if masks is None else torch.as_tensor(masks[:, r0:r1].astype(np.float64), device=dev)
+    D, P, eps = data.dim, cfg.n_slices, cfg.sigmoid_eps
+    w = torch.as_tensor(init.w, dtype=f64, device=dev).clone()
+    ws = None if init.ws is None else torch.as_tensor(init.ws, dtype=f64, device=dev).clone()
+    delta = None if init.delta_w is None else torch.as_tensor(init.delta_w, dtype=f64, device=dev).clone()
+    accs, bsz = [], []
+    local_algo = cfg.algo in ("ma", "bmuf", "easgd")
+
+    def gather_sum(contrib: torch.Tensor) -> torch.Tensor:
+        """contrib [P, D+1] with only local rows filled; partition-ordered sum across ranks (A.3)."""
+        dist.all_reduce_sum(contrib)            # rows are disjoint across ranks: this is a gather
+        acc = contrib[0].clone()
+        for p in range(1, P):
+            acc = acc + contrib[p]
+        return acc
+
+    for t in range(cfg.n_iterations):
+        contrib = torch.zeros(P, D + 1, dtype=f64, device=dev)
+        if local_algo and cfg.algo != "easgd":
+            ws = w.repeat(P, 1)
+        for li, p in enumerate(parts):
+            Xp, yp = X[loc[li]:loc[li + 1]], y[loc[li]:loc[li + 1]]
+            keep = torch.ones_like(yp) if m is None else m[t, loc[li]:loc[li + 1]]
+            cnt = keep.sum()
+            if not local_algo:
+                r = (_sigmoid(Xp @ w, eps) - yp) * keep
+                contrib[p, :D] = r @ Xp
+            else:
+                wp = ws[p]
+                n_inner = 1 if cfg.algo == "easgd" else cfg.n_local_iterations
+                if cnt.item() > 0:
+                    for _ in range(n_inner):
+                        r = (_sigmoid(Xp @ wp, eps) - yp) * keep
+                        g_mean = (r @ Xp) / cnt
+                        nw = wp - cfg.eta * g_mean
+                        if cfg.algo == "easgd":
+                            nw = nw - cfg.alpha * (wp - w)
+                        wp = nw
+                ws[p] = wp
+                contrib[p, :D] = wp
+            contrib[p, D] = cnt
+        S = gather_sum(contrib)
+        cnt_tot = float(S[D].item())
+        S = S[:D]
+        if cfg.algo == "ssgd":
+            if cnt_tot > 0:
+                reg = _reg_gradient_t(w, cfg.reg_type, cfg.reg_alpha)
+                w = w - cfg.eta * (S / cnt_tot + cfg.lam * reg)
+        elif cfg.algo == "gd":
+            w = w - cfg.eta * S
+        elif cfg.algo == "ma":
+            w = S / P
+        elif cfg.algo == "bmuf":
+            delta = cfg.mu * delta + cfg.zeta * (S / P - w)
+            w = w + delta
+        else:
+            w = (1 - cfg.beta) * w + cfg.beta * S / P
+        pred = (_sigmoid(Xt @ w, eps) >= 0.5).to(torch.int64)
+        accs.append(float((pred == yt).double().mean().item()))
+        bsz.append(int(cnt_tot))
+    ws_out = None
+    if ws is not None:
+        full = torch.zeros(P, D, dtype=f64, device=dev)
+        for p in parts:
+            full[p] = ws[p]
+        dist.all_reduce_sum(full)
+        ws_out = full.cpu().numpy()
+    return LogisticResult(w=w.cpu().numpy(), accs=accs, batch_sizes=bsz, ws=ws_out,
+                          delta_w=None if delta is None else delta.cpu().numpy())
+
+
+def _reg_gradient_t(w, reg_type, alpha):
+    if reg_type == "none":
+        return torch.zeros_like(w)
+    if reg_type == "l2":
+        return w
+    if reg_type == "l1":
+        return torch.sign(w)
+    return alpha * torch.sign(w) + (1 - alpha) * w
+
+
+# ------------------------------------------------------------------------------------------------ fused parity kernel
+def _run_fused_parity(data, cfg, init, dist, sh, masks, record_w) -> LogisticResult:
+    from ..parallel.symm import default_heap
+    lib = _native.load()
+    dev, f64 = dist.device, torch.float64
+    heap = default_heap()
+    parts = sh.local_partitions(dist.rank)
+    if not parts:
+        raise ValueError("fused parity path needs at least one partition per rank (n_slices >= world)")
+    r0, r1 = sh.local_row_range(dist.rank)
+    D, P, T = data.dim, cfg.n_slices, cfg.n_iterations
+    X = torch.as_tensor(np.ascontiguousarray(data.X_aug[r0:r1]), dtype=f64, device=dev)
+    y = torch.as_tensor(np.ascontiguousarray(data.y[r0:r1]), dtype=f64, device=dev)
+    off = torch.as_tensor(sh.local_offsets(dist.rank), dtype=torch.int64, device=dev)
+    Xt = torch.as_tensor(data.X_test_aug, dtype=f64, device=dev).contiguous()
+    yt = torch.as_tensor(data.y_test, dtype=torch.int32, device=dev).contiguous()
+    m = None if masks is None else torch.as_tensor(np.ascontiguousarray(masks[:, r0:r1]), dtype=torch.uint8, device=dev)
+    w = torch.as_tensor(init.w, dtype=f64, device=dev).clone()
+    ws = None
+    if cfg.algo in ("ma", "bmuf", "easgd"):
+        src = init.ws if init.ws is not None else np.tile(init.w, (P, 1))
+        ws = torch.as_tensor(np.ascontiguousarray(src[parts[0]:parts[-1] + 1]), dtype=f64, device=dev).clone()
+    delta = None
+    if cfg.algo == "bmuf":
+        delta = torch.as_tensor(init.delta_w if init.delta_w is not None else np.zeros(D), dtype=f64, device=dev).clone()
+    accs = torch.zeros(max(T, 1), dtype=f64, device=dev)
+    bsz = torch.zeros(max(T, 1), dtype=torch.int32, device=dev)
+    w_hist = torch.zeros(T, D, dtype=f64, device=dev) if record_w else None
+    reg = heap.region(f"lr_parity_P{P}_D{D}", int(lib.dapb_lr_parity_payload_bytes(P, D)), P)
+
+    a = _native.DapbLrParityArgs()
+    a.X, a.y, a.part_off, a.masks = X.data_ptr(), y.data_ptr(), off.data_ptr(), _native.ptr(m)
+    a.X_test, a.y_test = Xt.data_ptr(), yt.data_ptr()
+    a.n_local, a.n_test, a.D = r1 - r0, Xt.shape[0], D
+    a.P_local, a.P_global, a.part_base, a.T = len(parts), P, parts[0], T
+    a.algo, a.n_local_iters = _native.ALGO_ID[cfg.algo], cfg.n_local_iterations
+    a.reg_type = _native.REG_ID[cfg.reg_type]
+    a.max_part_rows = int(np.max(sh.sizes()))
+    a.eta, a.lam, a.reg_alpha, a.mu, a.zeta = cfg.eta, cfg.lam, cfg.reg_alpha, cfg.mu, cfg.zeta
+    a.alpha, a.beta, a.eps = cfg.alpha, cfg.beta, cfg.sigmoid_eps
+    a.w, a.ws, a.delta_w = w.data_ptr(), _native.ptr(ws), _native.ptr(delta)
+    a.accs, a.batch_sizes, a.w_hist = accs.data_ptr(), bsz.data_ptr(), _native.ptr(w_hist)
+    a.payload_off, a.flag_base, a.epoch_base = reg.payload_off, reg.flag_base, reg.epoch
+    reg.epoch += T
+    _native.check(lib.dapb_lr_parity_run(C.byref(a), heap.comm_ref(), _native.stream_ptr()), "lr_parity_run")
+    torch.cuda.synchronize()
+    # accuracy / batch sizes live on the rank owning partition 0
+    if dist.world > 1:
+        dist.broadcast(accs, 0)
+        dist.broadcast(bsz, 0)
+        if w_hist is not None:
+            dist.broadcast(w_hist, 0)
+    ws_out = None
+    if ws is not None:
+        full = torch.zeros(P, D, dtype=f64, device=dev)
+        full[parts[0]:parts[-1] + 1] = ws
+        dist.all_reduce_sum(full)
+        ws_out = full.cpu().numpy()
+    res = LogisticResult(w=w.cpu().numpy(), accs=accs[:T].cpu().tolist(), batch_sizes=bsz[:T].cpu().tolist(),
+                         ws=ws_out, delta_w=None if delta is None else delta.cpu().numpy())
+    if w_hist is not None:
+        res.w_hist = w_hist.cpu().numpy()
+    return res
+
+
+# ================================================================================================
+# Benchmark-scale engine: resident shard, one fused launch per optimiser step
+# ================================================================================================
+_DTYPE_ID = {torch.float32: 0, torch.bfloat16: 1}
+
+
+class ShardedLogisticEngine:
+    """Per-rank engine over a resident ``[n_rows, D]`` shard (bias column included).
+
+    One logical partition / replica per rank (``n_slices == world``: BASELINE.json config 2,
+    "8 workers on 8xB200").  ``backend='fused'`` launches ``dapb_lr_step`` once per local step;
+    ``backend='nccl'`` is the straightforward ``torch.matmul`` + ``dist.all_reduce`` baseline fed the
+    same Philox masks.
+    """
+
+    def __init__(self, X: torch.Tensor, y: torch.Tensor, cfg: LogisticConfig, row_base: int = 0,
+                 dist: Optional[Dist] = None, backend: str = "fused", w0: Optional[torch.Tensor] = None,
+                 grid: int = 0, heap=None):
+        self.dist = dist or current()
+        self.cfg, self.backend = cfg, backend
+        assert X.dim() == 2 and X.is_contiguous() and X.dtype in _DTYPE_ID
+        self.X, self.y = X, y.float().contiguous()
+        self.n_rows, self.D = X.shape
+        self.row_base = int(row_base)
+        dev = X.device
+        g = torch.Generator(device="cpu").manual_seed(cfg.seed if cfg.seed is not None else 0)
+        if w0 is None:
+            w0 = (2 * torch.rand(self.D, generator=g) - 1) * 0.01
+        self.w = w0.to(device=dev, dtype=torch.float32).clone().contiguous()
+        self.w_local = self.w.clone()
+        self.delta_w = torch.zeros_like(self.w)
+        self.t = 0
+        self.P = self.dist.world
+        self.threshold24 = (1 << 24) if cfg.algo == "gd" else bernoulli_threshold(cfg.mini_batch_fraction)
+        self.last_count = torch.zeros(1, dtype=torch.int32, device=dev)
+        if backend == "fused":
+            from ..parallel.symm import default_heap
+            self.lib = _native.load()
+            self.heap = heap or default_heap()
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            self.grid = grid or 2 * sms
+            self.partials = torch.empty(self.grid, self.D, dtype=torch.float32, device=dev)
+            self.counts = torch.zeros(self.grid, dtype=torch.int32, device=dev)
+            self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)
+            self.g = torch.zeros(self.D, dtype=torch.float32, device=dev)
+            self.region = self.heap.region(f"lr_step_D{self.D}", 2 * _native.MAX_RANKS * (self.D + 8) * 4, _native.MAX_RANKS)
+            self._eval_scratch = torch.zeros(2, dtype=torch.int32, device=dev)
+            self._acc = torch.zeros(1, dtype=torch.float32, device=dev)
+            self._args = self._base_args()
+
+    # ------------------------------------------------------------------ fused
+    def _base_args(self) -> _native.DapbLrStepArgs:
+        cfg, a = self.cfg, _native.DapbLrStepArgs()
+        a.X, a.y, a.n_rows, a.row_base = self.X.data_ptr(), self.y.data_ptr(), self.n_rows, self.row_base
+        a.D, a.dtype, a.mask = self.D, _DTYPE_ID[self.X.dtype], 0
+        a.seed, a.threshold24, a.eps = cfg.sample_seed, self.threshold24, cfg.sigmoid_eps
+        a.partials, a.counts, a.ticket, a.grid = self.partials.data_ptr(), self.counts.data_ptr(), self.ticket.data_ptr(), self.grid
+        a.algo, a.reg_type, a.use_sum = _native.ALGO_ID[cfg.algo], _native.REG_ID[cfg.reg_type], int(cfg.algo == "gd")
+        a.eta, a.lam, a.reg_alpha, a.mu, a.zeta = cfg.eta, cfg.lam, cfg.reg_alpha, cfg.mu, cfg.zeta
+        a.alpha = cfg.eta * cfg.rho
+        a.beta = self.P * cfg.eta * cfg.rho
+        a.n_replicas_total = self.P
+        a.g_out, a.cnt_out = self.g.data_ptr(), self.last_count.data_ptr()
+        a.w, a.w_local, a.delta_w = self.w.data_ptr(), self.w_local.data_ptr(), self.delta_w.data_ptr()
+        a.payload_off, a.flag_base = self.region.payload_off, self.region.flag_base
+        return a
+
+    def _launch(self, fin: int, w_fwd: torch.Tensor, iteration: int, reset: int = 0, stream=None):
+        a = self._args
+        a.fin, a.w_fwd, a.iteration, a.reset_replica = fin, w_fwd.data_ptr(), iteration, reset
+        if fin in (_native.FIN_SSGD, _native.FIN_LOCAL_SYNC):
+            a.epoch = self.region.next_epoch()
+        _native.check(self.lib.dapb_lr_step(C.byref(a), self.heap.comm_ref(), _native.stream_ptr(stream)), "lr_step")
+
+    def step(self, stream=None):
+        """One outer iteration / communication round of ``cfg.algo`` (ref loop bodies cited above)."""
+        cfg, t = self.cfg, self.t
+        if self.backend == "nccl":
+            self._step_nccl()
+        elif cfg.algo in ("ssgd", "gd"):
+            self._launch(_native.FIN_SSGD, self.w, t, stream=stream)
+        else:
+            n_inner = 1 if cfg.algo == "easgd" else cfg.n_local_iterations
+            for li in range(n_inner):                     # same mini-batch every local step (ma.py:99)
+                last = li == n_inner - 1
+                self._launch(_native.FIN_LOCAL_SYNC if last else _native.FIN_LOCAL, self.w_local, t,
+                             reset=int(cfg.algo != "easgd"), stream=stream)
+        self.t += 1
+
+    def evaluate(self, X_test: torch.Tensor, y_test: torch.Tensor) -> torch.Tensor:
+        """Accuracy of the current global ``w`` on a (replicated) test set; stays on device."""
+        if self.backend == "fused":
+            _native.check(self.lib.dapb_lr_eval(X_test.data_ptr(), y_test.data_ptr(), X_test.shape[0], self.D,
+                                                _DTYPE_ID[X_test.dtype], self.w.data_ptr(), float(self.cfg.sigmoid_eps),
+                                                self._acc.data_ptr(), self._eval_scratch.data_ptr(),
+                                                _native.stream_ptr()), "lr_eval")
+            return self._acc
+        z = X_test.float() @ self.w
+        pred = (1.0 / (torch.exp(-z) + 1.0 + self.cfg.sigmoid_eps) >= 0.5).float()
+        return (pred == y_test.float()).float().mean().reshape(1)
+
+    # ------------------------------------------------------------------ NCCL baseline
+    def _grad_nccl(self, w: torch.Tensor, keep: torch.Tensor):
+        idx = keep.nonzero(as_tuple=False).squeeze(1)
+        Xs = self.X.index_select(0, idx)
+        ys = self.y.index_select(0, idx)
+        z = (Xs @ w.to(Xs.dtype)).float()
+        r = 1.0 / (torch.exp(-z) + 1.0 + self.cfg.sigmoid_eps) - ys
+        g = (r.to(Xs.dtype) @ Xs).float()
+        return g, idx.numel()
+
+    def _step_nccl(self):
+        cfg, d = self.cfg, self.dist
+        if cfg.algo == "gd":
+            keep = torch.ones(self.n_rows, dtype=torch.bool, device=self.X.device)
+        else:
+            keep = philox_row_mask_torch(self.n_rows, cfg.mini_batch_fraction, cfg.sample_seed, self.t,
+                                         self.row_base, device=self.X.device)
+        if cfg.algo in ("ssgd", "gd"):
+            g, cnt = self._grad_nccl(self.w, keep)
+            buf = torch.cat([g, torch.tensor([float(cnt)], device=g.device)])
+            d.all_reduce_sum(buf)
+            g, cnt_tot = buf[:-1], float(buf[-1].item())
+            if cfg.algo == "gd":
+                self.w -= cfg.eta * g
+            elif cnt_tot > 0:
+                self.w -= cfg.eta * (g / cnt_tot + cfg.lam * _reg_gradient_t(self.w, cfg.reg_type, cfg.reg_alpha))
+            self.last_count.fill_(int(cnt_tot))
+            return
+        alpha, beta = cfg.eta * cfg.rho, self.P * cfg.eta * cfg.rho
+        if cfg.algo != "easgd":
+            self.w_local.copy_(self.w)
+        n_inner = 1 if cfg.algo == "easgd" else cfg.n_local_iterations
+        for _ in range(n_inner):
+            g, cnt = self._grad_nccl(self.w_local, keep)
+            if cnt > 0:
+                nw = self.w_local - cfg.eta * g / cnt
+                if cfg.algo == "easgd":
+                    nw = nw - alpha * (self.w_local - self.w)
+                self.w_local.copy_(nw)
+        S = self.w_local.clone()
+        d.all_reduce_sum(S)
+        if cfg.algo == "ma":
+            self.w.copy_(S / self.P)
+        elif cfg.algo == "bmuf":
+            self.delta_w.copy_(cfg.mu * self.delta_w + cfg.zeta * (S / self.P - self.w))
+            self.w += self.delta_w
+        else:
+            self.w.copy_((1 - beta) * self.w + beta * S / self.P)

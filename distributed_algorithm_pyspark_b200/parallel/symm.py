@@ -1,0 +1,147 @@
+"""Symmetric heap over NVLink peer memory (host side of csrc/comm.cuh).
+
+Each rank ``cudaMalloc``s one heap (flags in the first 64 KiB, payload after), the CUDA IPC
+handles are exchanged once through ``torch.distributed`` (bootstrap only) and every peer heap is
+mapped into every process.  Kernels then push data straight into peer memory; NCCL is not on any
+hot path.  Regions are handed out by a bump allocator that every rank drives identically, so an
+offset means the same thing everywhere ("symmetric").
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Dict, Optional
+
+import torch
+
+from .. import _native
+from .dist import Dist, current
+
+
+@dataclass
+class Region:
+    """A symmetric allocation: payload offset + a private range of flag words + an epoch counter."""
+    payload_off: int
+    nbytes: int
+    flag_base: int
+    n_flags: int
+    epoch: int = 0
+
+    def next_epoch(self) -> int:
+        self.epoch += 1
+        return self.epoch
+
+
+class SymmetricHeap:
+    def __init__(self, nbytes: int = 64 << 20, dist: Optional[Dist] = None):
+        self.dist = dist or current()
+        self.lib = _native.load()
+        self.nbytes = int(nbytes)
+        base = C.c_void_p()
+        _native.check(self.lib.dapb_symm_alloc(self.nbytes, C.byref(base)), "symm_alloc")
+        self.base = base.value
+        self._peer_ptrs = [None] * self.dist.world
+        self._peer_ptrs[self.dist.rank] = self.base
+        self._payload_top = 0
+        self._flag_top = 0
+        self._regions: Dict[str, Region] = {}
+        if self.dist.world > 1:
+            handle = (C.c_ubyte * 64)()
+            _native.check(self.lib.dapb_ipc_get_handle(self.base, handle), "ipc_get_handle")
+            handles = self.dist.all_gather_object(bytes(handle))
+            for r, h in enumerate(handles):
+                if r == self.dist.rank:
+                    continue
+                buf = (C.c_ubyte * 64).from_buffer_copy(h)
+                out = C.c_void_p()
+                _native.check(self.lib.dapb_ipc_open_handle(buf, C.byref(out)), f"ipc_open_handle(rank {r})")
+                self._peer_ptrs[r] = out.value
+            self.dist.barrier()
+        self.comm = _native.DapbComm()
+        self.comm.rank = self.dist.rank
+        self.comm.world = self.dist.world
+        self.comm.heap_bytes = self.nbytes
+        for r in range(self.dist.world):
+            self.comm.heap[r] = self._peer_ptrs[r]
+
+    # ------------------------------------------------------------------ allocation
+    def region(self, name: str, nbytes: int, n_flags: int) -> Region:
+        """Named symmetric region (idempotent).  Every rank must request regions in the same order."""
+        if name in self._regions:
+            reg = self._regions[name]
+            if reg.nbytes < nbytes or reg.n_flags < n_flags:
+                raise ValueError(f"region {name!r} exists with a smaller size")
+            return reg
+        off = (self._payload_top + 255) & ~255
+        if _native.FLAG_BYTES + off + nbytes > self.nbytes:
+            raise MemoryError(f"symmetric heap exhausted: need {nbytes} B at {off}, heap {self.nbytes} B")
+        if (self._flag_top + n_flags) * 8 > _native.FLAG_BYTES:
+            raise MemoryError("symmetric heap flag words exhausted")
+        reg = Region(off, nbytes, self._flag_top, n_flags)
+        self._payload_top = off + nbytes
+        self._flag_top += n_flags
+        self._regions[name] = reg
+        return reg
+
+    def payload_ptr(self, reg: Region, rank: Optional[int] = None) -> int:
+        r = self.dist.rank if rank is None else rank
+        return self._peer_ptrs[r] + _native.FLAG_BYTES + reg.payload_off
+
+    def tensor(self, reg: Region, shape, dtype) -> torch.Tensor:
+        """Local view of a region as a torch tensor (zero-copy, device memory owned by the heap)."""
+        n = 1
+        for s in shape:
+            n *= int(s)
+        itemsize = torch.empty((), dtype=dtype).element_size()
+        assert n * itemsize <= reg.nbytes
+        ptr = self.payload_ptr(reg)
+        arr = _CudaArray(ptr, tuple(int(s) for s in shape), dtype)
+        return torch.as_tensor(arr, device=self.dist.device)
+
+    def comm_ref(self):
+        return C.byref(self.comm)
+
+    def close(self):
+        if self.base is None:
+            return
+        torch.cuda.synchronize()
+        if self.dist.world > 1:
+            self.dist.barrier()
+            for r, p in enumerate(self._peer_ptrs):
+                if r != self.dist.rank and p:
+                    self.lib.dapb_ipc_close_handle(p)
+            self.dist.barrier()
+        self.lib.dapb_symm_free(self.base)
+        self.base = None
+
+
+_TYPESTR = {torch.float32: "<f4", torch.float64: "<f8", torch.int32: "<i4", torch.int64: "<i8",
+            torch.uint8: "|u1", torch.float16: "<f2", torch.int16: "<i2"}
+
+
+class _CudaArray:
+    """Minimal __cuda_array_interface__ carrier so torch can wrap raw heap memory."""
+
+    def __init__(self, ptr: int, shape, dtype):
+        if dtype == torch.bfloat16:
+            raise TypeError("wrap bf16 regions as int16 and .view(torch.bfloat16)")
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": _TYPESTR[dtype], "data": (ptr, False),
+                                         "version": 2, "strides": None}
+
+
+_DEFAULT: Optional[SymmetricHeap] = None
+
+
+def default_heap(nbytes: int = 64 << 20) -> SymmetricHeap:
+    """Process-wide heap, created on first use (collective across ranks!)."""
+    global _DEFAULT
+    if _DEFAULT is None:
+        _DEFAULT = SymmetricHeap(nbytes)
+    return _DEFAULT
+
+
+def reset_default_heap():
+    global _DEFAULT
+    if _DEFAULT is not None:
+        _DEFAULT.close()
+    _DEFAULT = None

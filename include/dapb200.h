@@ -1,0 +1,147 @@
+/* dapb200 -- C ABI of the B200-native (sm_100a) kernels behind distributed_algorithm_pyspark_b200.
+ *
+ * Every entry point returns 0 on success, a cudaError_t (> 0) or DAPB_ERR_* (< 0) otherwise;
+ * dapb_last_error() returns the message of the last failure on the calling thread.
+ * Pointers are device pointers unless a comment says "host".  `stream` is a cudaStream_t.
+ * Citations "ref:" point at /root/reference (orion-orion/Distributed-Algorithm-PySpark).
+ */
+#ifndef DAPB200_H_
+#define DAPB200_H_
+
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define DAPB_API __attribute__((visibility("default")))
+#else
+#define DAPB_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DAPB_MAX_RANKS 8
+#define DAPB_FLAG_BYTES 65536ull          /* first 64 KiB of every symmetric heap = uint64 flags */
+#define DAPB_WAIT_TIMEOUT_NS 20000000000ull
+
+#define DAPB_ERR_INVALID (-1)
+#define DAPB_ERR_UNSUPPORTED (-2)
+
+/* Symmetric-heap view handed to kernels that communicate (csrc/comm.cuh).
+ * heap[r] = base of rank r's heap as mapped into THIS process; heap[rank] is local memory. */
+typedef struct DapbComm {
+  int32_t rank;
+  int32_t world;
+  void* heap[DAPB_MAX_RANKS];
+  uint64_t heap_bytes;
+} DapbComm;
+
+/* ------------------------------------------------------------------ runtime ------------ */
+DAPB_API const char* dapb_last_error(void);
+DAPB_API int dapb_version(void);
+DAPB_API int dapb_device_info(int32_t* sm_count, int32_t* cc_major, int32_t* cc_minor, uint64_t* total_mem);
+/* Symmetric heap: cudaMalloc'ed (not from a caching allocator, so IPC handles map 1:1), zeroed. */
+DAPB_API int dapb_symm_alloc(uint64_t bytes, void** out);
+DAPB_API int dapb_symm_free(void* ptr);
+DAPB_API int dapb_ipc_get_handle(void* ptr, void* handle64 /* host, 64 bytes */);
+DAPB_API int dapb_ipc_open_handle(const void* handle64 /* host */, void** out);
+DAPB_API int dapb_ipc_close_handle(void* ptr);
+/* F8 self-test: `world` CTAs of ONE cooperative launch act as ranks over `world` heaps carved
+ * from `heaps` (each heap_bytes long); runs `iters` all-reduces of n floats and checks them.
+ * out_fail (device int32) receives the number of mismatching elements. */
+DAPB_API int dapb_comm_selftest(void* heaps, uint64_t heap_bytes, int32_t world, int32_t n, int32_t iters,
+                       int32_t* out_fail, void* stream);
+/* Stand-alone F8 collectives (tests / baselines; production kernels inline them).
+ * One CTA per rank; every rank must call with the same epoch (strictly increasing per flag_base). */
+DAPB_API int dapb_allreduce_f32(const DapbComm* comm, uint64_t payload_off, uint32_t flag_base,
+                       uint64_t epoch, const float* src, float* dst, int32_t n, void* stream);
+DAPB_API int dapb_allreduce_f64(const DapbComm* comm, uint64_t payload_off, uint32_t flag_base,
+                       uint64_t epoch, const double* src, double* dst, int32_t n, void* stream);
+DAPB_API int dapb_barrier(const DapbComm* comm, uint32_t flag_base, uint64_t epoch, void* stream);
+
+/* ------------------------------------------------------------------ F1/F2 logistic -------
+ * ref: optimization/ssgd.py:23-33,93-112; machine_learning/logistic_regression.py:76-92;
+ *      optimization/ma.py:93-113; optimization/bmuf.py:98-121; optimization/easgd.py:95-113 */
+enum { DAPB_LR_SSGD = 0, DAPB_LR_GD = 1, DAPB_LR_MA = 2, DAPB_LR_BMUF = 3, DAPB_LR_EASGD = 4 };
+enum { DAPB_REG_NONE = 0, DAPB_REG_L2 = 1, DAPB_REG_L1 = 2, DAPB_REG_ELASTIC = 3 };
+
+/* Whole training loop of the reference's default (small, fp64) configuration in ONE persistent
+ * cooperative kernel: one CTA per logical partition, per-iteration exchange through the
+ * symmetric heap (in-kernel all-reduce, partition-ordered sum), test accuracy on device. */
+typedef struct DapbLrParityArgs {
+  const double* X;          /* [n_local, D] rows of this rank's partitions, bias column included */
+  const double* y;          /* [n_local] */
+  const int64_t* part_off;  /* [P_local + 1] local row offsets */
+  const uint8_t* masks;     /* [T, n_local] keep flags (ref ssgd.py:97 sampler), NULL = all rows */
+  const double* X_test;     /* [n_test, D] */
+  const int32_t* y_test;    /* [n_test] */
+  int64_t n_local;
+  int32_t n_test, D, P_local, P_global, part_base, T;
+  int32_t algo, n_local_iters, reg_type, max_part_rows;
+  double eta, lam, reg_alpha, mu, zeta, alpha, beta, eps;
+  double* w;                /* [D] in/out (replicated) */
+  double* ws;               /* [P_local, D] in/out replicas (EASGD persists them, ref easgd.py:88) */
+  double* delta_w;          /* [D] in/out (BMUF, ref bmuf.py:95) */
+  double* accs;             /* [T] out, written by the rank owning partition 0 */
+  int32_t* batch_sizes;     /* [T] out */
+  double* w_hist;           /* [T, D] out or NULL */
+  uint64_t payload_off;     /* needs 2*P_global*(D+1) doubles */
+  uint32_t flag_base;       /* needs P_global flags */
+  uint64_t epoch_base;      /* flags must be < epoch_base+1 on entry; kernel uses epoch_base+t+1 */
+} DapbLrParityArgs;
+DAPB_API int dapb_lr_parity_run(const DapbLrParityArgs* args, const DapbComm* comm, void* stream);
+DAPB_API uint64_t dapb_lr_parity_payload_bytes(int32_t P_global, int32_t D);
+
+/* One optimiser step at benchmark scale, ONE launch: Bernoulli row sample (Philox or explicit
+ * mask) -> forward z = Xw -> r = sigmoid(z) - y -> backward g = X^T r -> deterministic grid
+ * reduction -> [last CTA] in-kernel all-reduce over NVLink peers -> optimiser update. */
+enum { DAPB_LR_FIN_GRAD_ONLY = 0,   /* g_out[D], cnt_out only                                  */
+       DAPB_LR_FIN_SSGD = 1,        /* all-reduce(g,cnt); w -= eta*(g/cnt + lam*reg(w))  (or sum: GD) */
+       DAPB_LR_FIN_LOCAL = 2,       /* w_p -= eta*g/cnt + alpha*(w_p - centre)                 */
+       DAPB_LR_FIN_LOCAL_SYNC = 3   /* LOCAL, then all-reduce(w_p) + MA / BMUF / EASGD rule    */ };
+typedef struct DapbLrStepArgs {
+  const void* X;            /* [n_rows, D] row-major, dtype 0 = fp32, 1 = bf16 */
+  const float* y;           /* [n_rows] */
+  int64_t n_rows;
+  int64_t row_base;         /* global index of row 0 (Philox counter) */
+  int32_t D, dtype;
+  const uint8_t* mask;      /* optional explicit keep flags [n_rows]; NULL -> Philox */
+  uint64_t seed;
+  uint32_t iteration;
+  uint32_t threshold24;     /* keep iff (philox>>8) < threshold24; >= 1<<24 keeps every row */
+  float eps;                /* sigmoid variant (ref ma.py:26) */
+  const float* w_fwd;       /* [D] weights used in the forward pass (replica or global) */
+  /* scratch (caller-allocated, reusable): */
+  float* partials;          /* [grid, D] */
+  int32_t* counts;          /* [grid] */
+  uint32_t* ticket;         /* 1 word, zero before first use */
+  int32_t grid;             /* CTAs to launch (0 = 2 per SM) */
+  /* finalize */
+  int32_t fin, algo, reg_type, use_sum;   /* use_sum=1: GD (ref logistic_regression.py:85) */
+  float eta, lam, reg_alpha, mu, zeta, alpha, beta;
+  int32_t n_replicas_total; /* P (= n_slices) for the model average */
+  float* g_out;             /* [D]  (GRAD_ONLY; also receives the reduced gradient otherwise) */
+  int32_t* cnt_out;         /* [1]  global sampled count of this step */
+  float* w;                 /* [D] in/out global / centre weights */
+  float* w_local;           /* [D] in/out replica (LOCAL / LOCAL_SYNC) */
+  float* delta_w;           /* [D] in/out (BMUF) */
+  int32_t reset_replica;    /* LOCAL_SYNC: copy new w into w_local (MA/BMUF, ref ma.py:96) */
+  uint64_t payload_off;     /* needs 2*world*(D+4) floats */
+  uint32_t flag_base;       /* needs `world` flags */
+  uint64_t epoch;           /* strictly increasing per call on this flag_base */
+} DapbLrStepArgs;
+DAPB_API int dapb_lr_step(const DapbLrStepArgs* args, const DapbComm* comm, void* stream);
+/* Test-set accuracy with the reference's 0.5 threshold (ref ssgd.py:107-110). acc_out: [1] float. */
+DAPB_API int dapb_lr_eval(const void* X, const float* y, int64_t n_rows, int32_t D, int32_t dtype,
+                 const float* w, float eps, float* acc_out, uint32_t* scratch2, void* stream);
+
+/* ------------------------------------------------------------------ F7 Monte-Carlo pi ----
+ * ref: randomized_algorithm/monte_carlo.py:17-31.  Sample i in [first, first+n) comes from
+ * Philox counter i/2; a point is accepted iff x^2+y^2 <= 1 evaluated exactly in integers.
+ * count_io (device uint64) is atomically incremented. */
+DAPB_API int dapb_mc_pi(uint64_t first, uint64_t n, uint64_t seed, unsigned long long* count_io, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DAPB200_H_ */
