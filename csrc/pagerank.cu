@@ -1,0 +1,162 @@
+// F4 -- PageRank: CSR(A^T) SpMV fused with the damping / teleport update and with the all-gather of
+// the contribution vector (every finished entry is pushed straight into every peer's copy over
+// NVLink; no separate collective, no host round trip).
+//
+// ref: graph_computation/pagerank.py:21-25 (computeContribs: rank / out-degree to every neighbour),
+//      :52-57 (join, flatMap, reduceByKey(add), mapValues(q/n + (1-q)*rank)).
+// Reference quirks kept: n = number of distinct SOURCE vertices; a vertex that
+// receives no contribution in an iteration disappears (rank 0, contributes nothing afterwards);
+// sinks receive rank but their mass is dropped.  Vector form:
+//      s[v] = sum_{u->v} c[u];  r[v] = s[v] > 0 ? q/n + (1-q) s[v] : 0;  c'[v] = r[v] / outdeg[v].
+//
+// Sharding: rank g owns destination vertices [v0, v1) and the CSR rows of A^T for them; the
+// contribution vector c (all V entries) is replicated in the symmetric heap, double-buffered on the
+// iteration parity: iteration t reads buffer t&1 and pushes into buffer (t+1)&1 of every rank.
+#include "comm.cuh"
+
+using namespace dapb;
+
+namespace {
+
+constexpr int kPrThreads = 256;
+constexpr int kGroup = 8;            // lanes per light row
+
+struct PrArgs {
+  const int64_t* row_ptr;   // [nv_local + 1], offsets into col_idx
+  const int32_t* col_idx;   // [nnz_local] source vertex ids (global)
+  const float* inv_outdeg;  // [nv_local] 1/outdeg of the OWNED vertices (0 for sinks)
+  const int32_t* heavy;     // [n_heavy] local row ids with degree >= heavy threshold (may be null)
+  int32_t n_heavy, heavy_threshold;
+  int64_t nv_local, v0, V;
+  float base, damp;         // q/n and (1-q)
+  float* ranks_local;       // [nv_local] out
+  uint64_t c_off;           // payload offset of the double-buffered contribution vector [2][V] float
+  uint32_t flag_base;       // `world` flags
+  uint64_t epoch;           // iteration number, starts at 1
+  uint32_t* ticket;
+  int32_t wait_prev;        // wait for epoch-1 from every rank before reading
+};
+
+__device__ __forceinline__ void pr_finish_row(const PrArgs& a, const DapbComm& c, float* c_next_local,
+                                               int64_t row, float s) {
+  const float r = s > 0.f ? a.base + a.damp * s : 0.f;          // ref pagerank.py:57 + presence rule
+  a.ranks_local[row] = r;
+  const float cn = r * a.inv_outdeg[row];                        // ref pagerank.py:21-25
+  const int64_t v = a.v0 + row;
+  if (c.world == 1) {
+    c_next_local[v] = cn;
+  } else {
+#pragma unroll 1
+    for (int g = 0; g < c.world; ++g)
+      reinterpret_cast<float*>(comm_payload(c, g, a.c_off))[((a.epoch & 1) * a.V) + v] = cn;
+  }
+}
+
+__global__ void __launch_bounds__(kPrThreads) pagerank_step_kernel(PrArgs a, DapbComm c) {
+  __shared__ float s_red[kPrThreads / 32];
+  __shared__ bool s_last;
+  const int tid = threadIdx.x;
+  // iteration `epoch` reads parity (epoch-1)&1 and writes parity epoch&1
+  const float* c_cur = reinterpret_cast<const float*>(comm_payload(c, c.rank, a.c_off)) + (((a.epoch - 1) & 1) * a.V);
+  float* c_next_local = reinterpret_cast<float*>(comm_payload(c, c.rank, a.c_off)) + ((a.epoch & 1) * a.V);
+
+  if (c.world > 1 && a.wait_prev) {                  // all peers' pushes of the previous iteration landed?
+    if (tid < c.world) comm_wait_flag(comm_flags(c, c.rank) + a.flag_base + tid, a.epoch - 1);
+    __syncthreads();
+  }
+
+  // ---- heavy rows first: one CTA per row, whole block strides over the row ----------------------
+  for (int h = blockIdx.x; h < a.n_heavy; h += gridDim.x) {
+    const int64_t row = a.heavy[h];
+    const int64_t e0 = a.row_ptr[row], e1 = a.row_ptr[row + 1];
+    float s = 0.f;
+    for (int64_t e = e0 + tid; e < e1; e += kPrThreads) s += __ldcg(c_cur + a.col_idx[e]);
+    s = warp_sum(s);
+    if ((tid & 31) == 0) s_red[tid >> 5] = s;
+    __syncthreads();
+    if (tid == 0) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < kPrThreads / 32; ++w) t += s_red[w];
+      pr_finish_row(a, c, c_next_local, row, t);
+    }
+    __syncthreads();
+  }
+
+  // ---- light rows: 8 lanes per row ---------------------------------------------------------------
+  const int sub = tid & (kGroup - 1);
+  const int64_t grp = ((int64_t)blockIdx.x * kPrThreads + tid) / kGroup;
+  const int64_t n_grp = (int64_t)gridDim.x * kPrThreads / kGroup;
+  for (int64_t row0 = 0; row0 < a.nv_local; row0 += n_grp) {
+    const int64_t row = row0 + grp;
+    const bool valid = row < a.nv_local;
+    int64_t e0 = 0, e1 = 0;
+    if (valid) { e0 = a.row_ptr[row]; e1 = a.row_ptr[row + 1]; }
+    const bool is_heavy = a.n_heavy > 0 && (e1 - e0) >= a.heavy_threshold;
+    float s = 0.f;
+    if (valid && !is_heavy)
+      for (int64_t e = e0 + sub; e < e1; e += kGroup) s += __ldcg(c_cur + a.col_idx[e]);
+#pragma unroll
+    for (int o = kGroup / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (valid && !is_heavy && sub == 0) pr_finish_row(a, c, c_next_local, row, s);
+  }
+
+  // ---- completion: last CTA tells every rank that this rank's slice of iteration `epoch` is in ----
+  __threadfence_system();
+  __syncthreads();
+  if (tid == 0) {
+    unsigned t = atomicAdd(a.ticket, 1u);
+    s_last = (t == gridDim.x - 1);
+    if (s_last) *a.ticket = 0;
+  }
+  __syncthreads();
+  if (!s_last || c.world == 1) return;
+  if (tid == 0) __threadfence_system();
+  __syncthreads();
+  if (tid < c.world) st_release_sys(comm_flags(c, tid) + a.flag_base + c.rank, a.epoch);
+}
+
+// contribution vector of iteration 0: c[v] = (1/n) / outdeg[v] for source vertices, written by the
+// owner of v into every rank's buffer 0 (ref pagerank.py:47).
+__global__ void pagerank_init_kernel(DapbComm c, const float* inv_outdeg, int64_t nv_local, int64_t v0, int64_t V,
+                                     float r0, uint64_t c_off) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv_local; i += (int64_t)gridDim.x * blockDim.x) {
+    const float io = inv_outdeg[i];
+    const float cn = io > 0.f ? r0 * io : 0.f;
+    for (int g = 0; g < c.world; ++g) reinterpret_cast<float*>(comm_payload(c, g, c_off))[v0 + i] = cn;
+  }
+}
+
+}  // namespace
+
+extern "C" int dapb_pagerank_init(const DapbComm* comm, const float* inv_outdeg, int64_t nv_local, int64_t v0,
+                                  int64_t V, float r0, uint64_t c_off, void* stream) {
+  DAPB_REQUIRE(comm && comm->world >= 1 && comm->world <= DAPB_MAX_RANKS, "pagerank_init: bad comm");
+  uint64_t need = DAPB_FLAG_BYTES + c_off + 2ull * V * sizeof(float);
+  DAPB_REQUIRE(need <= comm->heap_bytes, "pagerank_init: heap too small (%llu > %llu)", (unsigned long long)need,
+               (unsigned long long)comm->heap_bytes);
+  int blocks = (int)((nv_local + 255) / 256);
+  if (blocks > dapb::sm_count() * 8) blocks = dapb::sm_count() * 8;
+  if (blocks < 1) blocks = 1;
+  pagerank_init_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(*comm, inv_outdeg, nv_local, v0, V, r0, c_off);
+  DAPB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int dapb_pagerank_step(const DapbComm* comm, const int64_t* row_ptr, const int32_t* col_idx,
+                                  const float* inv_outdeg, const int32_t* heavy, int32_t n_heavy,
+                                  int32_t heavy_threshold, int64_t nv_local, int64_t v0, int64_t V, float base,
+                                  float damp, float* ranks_local, uint64_t c_off, uint32_t flag_base,
+                                  uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t grid, void* stream) {
+  DAPB_REQUIRE(comm && comm->world >= 1 && comm->world <= DAPB_MAX_RANKS, "pagerank_step: bad comm");
+  DAPB_REQUIRE(epoch >= 1 && ticket != nullptr, "pagerank_step: epoch starts at 1, ticket required");
+  PrArgs a;
+  a.row_ptr = row_ptr; a.col_idx = col_idx; a.inv_outdeg = inv_outdeg; a.heavy = heavy;
+  a.n_heavy = heavy ? n_heavy : 0; a.heavy_threshold = heavy_threshold;
+  a.nv_local = nv_local; a.v0 = v0; a.V = V; a.base = base; a.damp = damp; a.ranks_local = ranks_local;
+  a.c_off = c_off; a.flag_base = flag_base; a.epoch = epoch; a.ticket = ticket; a.wait_prev = wait_prev;
+  if (grid <= 0) grid = dapb::sm_count() * 8;
+  pagerank_step_kernel<<<grid, kPrThreads, 0, (cudaStream_t)stream>>>(a, *comm);
+  DAPB_LAUNCH_CHECK();
+  return 0;
+}

@@ -88,6 +88,21 @@ def _declare(lib: C.CDLL):
         "dapb_lr_step": (C.c_int, [P(DapbLrStepArgs), P(DapbComm), vp]),
         "dapb_lr_eval": (C.c_int, [vp, vp, i64, i32, i32, vp, f32, vp, vp, vp]),
         "dapb_mc_pi": (C.c_int, [u64, u64, u64, vp, vp]),
+        "dapb_kmeans_assign": (C.c_int, [vp, i64, i32, i32, vp, i32, vp, vp, vp, vp]),
+        "dapb_kmeans_finalize": (C.c_int, [P(DapbComm), vp, vp, vp, i32, i32, i32, u64, u32, u64, vp, i32, vp]),
+        "dapb_kmeans_payload_bytes": (u64, [i32, i32, i32, i32]),
+        "dapb_pagerank_init": (C.c_int, [P(DapbComm), vp, i64, i64, i64, f32, u64, vp]),
+        "dapb_pagerank_step": (C.c_int, [P(DapbComm), vp, vp, vp, vp, i32, i32, i64, i64, i64, f32, f32, vp,
+                                         u64, u32, u64, vp, i32, i32, vp]),
+        "dapb_tc_seed": (C.c_int, [vp, i64, vp, u64, vp, vp, i32, i32, vp]),
+        "dapb_tc_expand": (C.c_int, [P(DapbComm), vp, vp, vp, i64, vp, u64, vp, vp, u64, u64, vp]),
+        "dapb_tc_exchange": (C.c_int, [P(DapbComm), vp, u64, u64, u32, u64, vp]),
+        "dapb_tc_drain": (C.c_int, [P(DapbComm), vp, u64, vp, vp, u64, u64, vp]),
+        "dapb_gram": (C.c_int, [P(DapbComm), vp, vp, i64, i32, i32, i64, i64, i32, vp, i32, vp, vp, u64, u32, u64, i32, vp]),
+        "dapb_rows_times_small": (C.c_int, [vp, vp, i64, i32, i32, i64, i32, i32, vp, vp]),
+        "dapb_solve_rows": (C.c_int, [vp, f64, vp, i64, i32, i32, vp, vp]),
+        "dapb_sq_residual": (C.c_int, [vp, vp, vp, i64, i32, i32, i32, vp, vp]),
+        "dapb_cholesky": (C.c_int, [vp, i32, i32, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name, None)

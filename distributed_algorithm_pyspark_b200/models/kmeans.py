@@ -1,0 +1,146 @@
+"""Lloyd's k-means (reference: ``machine_learning/k-means.py``).
+
+Semantics kept from the reference: initial centres = ``takeSample(False, k, 42)`` (:53), ties go to the
+lowest centre index (:25), a cluster that receives no point keeps its centre (:70-71), a fixed number
+of iterations (``convergeDist`` is defined but unused, :16).
+
+Backends: ``oracle`` (NumPy), ``torch`` (``cdist``-style matmul + ``index_add_`` + ``all_reduce`` -- the
+NCCL baseline), ``fused`` (sm_100a: assignment kernel -- tcgen05 tensor-core version for the benchmark
+shape, CUDA-core version otherwise -- accumulating per-centroid sums, then ONE finalize kernel that
+fuses reduce-scatter, mean update and centroid all-gather over NVLink peer memory).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+import torch
+
+from .. import _native
+from ..config import KMeansConfig
+from ..oracle import spark_semantics as sp
+from ..oracle.algorithms import KMeansResult, kmeans_oracle
+from ..parallel.dist import Dist, current
+from ..parallel.partition import RowSharding
+
+_DT = {torch.float32: 0, torch.bfloat16: 1, torch.float64: 2}
+
+
+def initial_center_indices(n_points: int, cfg: KMeansConfig):
+    sizes = np.diff(sp.partition_offsets(n_points, cfg.n_slices))
+    return sp.take_sample_indices(sizes, cfg.k, cfg.seed)
+
+
+def run_kmeans(points: np.ndarray, cfg: KMeansConfig, backend: str = "auto", dist: Optional[Dist] = None,
+               init_centers: Optional[np.ndarray] = None) -> KMeansResult:
+    """Cluster a host array the way the reference script does (small / parity problems)."""
+    if backend == "auto":
+        backend = "fused" if _native.available() else "torch"
+    if backend == "oracle":
+        return kmeans_oracle(points, cfg, init_centers)
+    dist = dist or current()
+    pts = np.asarray(points, dtype=np.float64)
+    n = pts.shape[0]
+    idx = [] if init_centers is not None else initial_center_indices(n, cfg)
+    c0 = np.asarray(init_centers, dtype=np.float64) if init_centers is not None else pts[idx]
+    sh = RowSharding.spark(n, cfg.n_slices, dist.world)
+    r0, r1 = sh.local_row_range(dist.rank)
+    X = torch.as_tensor(np.ascontiguousarray(pts[r0:r1]), dtype=torch.float64, device=dist.device)
+    eng = ShardedKMeans(X, cfg.k, torch.as_tensor(c0, dtype=torch.float64, device=dist.device), dist=dist,
+                        backend="fused" if backend == "fused" else "nccl")
+    history = []
+    for _ in range(cfg.n_iterations):
+        eng.step()
+        history.append(eng.centers.cpu().numpy().copy())
+    assign_local = eng.assign()                                    # final centres (ref k-means.py:76, A.7)
+    parts = dist.all_gather_object(assign_local.cpu().numpy())
+    return KMeansResult(centers=eng.centers.cpu().numpy(), assignment=np.concatenate(parts).astype(np.int64),
+                        init_indices=list(idx), history=history)
+
+
+class ShardedKMeans:
+    """Per-rank k-means over a resident ``[n_local, d]`` shard; centres replicated on every rank."""
+
+    def __init__(self, X: torch.Tensor, k: int, centers: torch.Tensor, dist: Optional[Dist] = None,
+                 backend: str = "fused", use_tc: Optional[bool] = None, heap=None):
+        self.dist = dist or current()
+        self.backend = backend
+        assert X.dim() == 2 and X.is_contiguous() and X.dtype in _DT
+        self.X, self.k = X, int(k)
+        self.n, self.d = X.shape
+        self.acc_dtype = torch.float64 if X.dtype == torch.float64 else torch.float32
+        self.centers = centers.to(device=X.device, dtype=self.acc_dtype).clone().contiguous()
+        self.counts_out = torch.zeros(self.k, dtype=torch.int32, device=X.device)
+        self.iteration = 0
+        if backend == "fused":
+            from ..parallel.symm import default_heap
+            self.lib = _native.load()
+            self.heap = heap or default_heap()
+            self.sums = torch.zeros(self.k, self.d, dtype=self.acc_dtype, device=X.device)
+            self.counts = torch.zeros(self.k, dtype=torch.int32, device=X.device)
+            eb = 8 if self.acc_dtype == torch.float64 else 4
+            nbytes = int(self.lib.dapb_kmeans_payload_bytes(self.dist.world, self.k, self.d, eb))
+            self.region = self.heap.region(f"kmeans_k{self.k}_d{self.d}_{eb}", max(nbytes, 256), 2 * _native.MAX_RANKS)
+            from ..ops import kmeans_tc
+            self.tc = None
+            if use_tc is None:
+                use_tc = kmeans_tc.supported(self.X, self.k)
+            if use_tc:
+                self.tc = kmeans_tc.KMeansTC(self.X, self.k)
+
+    def step(self):
+        """One Lloyd iteration (ref k-means.py:55-71)."""
+        if self.backend == "fused":
+            st = _native.stream_ptr()
+            if self.tc is not None:
+                self.tc.assign_accumulate(self.centers, self.sums, self.counts)
+            else:
+                _native.check(self.lib.dapb_kmeans_assign(self.X.data_ptr(), self.n, self.d, _DT[self.X.dtype],
+                                                          self.centers.data_ptr(), self.k, 0, self.sums.data_ptr(),
+                                                          self.counts.data_ptr(), st), "kmeans_assign")
+            _native.check(self.lib.dapb_kmeans_finalize(self.heap.comm_ref(), self.sums.data_ptr(), self.counts.data_ptr(),
+                                                        self.centers.data_ptr(), self.k, self.d,
+                                                        int(self.acc_dtype == torch.float64), self.region.payload_off,
+                                                        self.region.flag_base, self.region.next_epoch(),
+                                                        self.counts_out.data_ptr(), 1, st), "kmeans_finalize")
+        else:
+            a = self._assign_torch()
+            sums = torch.zeros(self.k, self.d, dtype=self.acc_dtype, device=self.X.device)
+            sums.index_add_(0, a, self.X.to(self.acc_dtype))
+            cnt = torch.bincount(a, minlength=self.k).to(self.acc_dtype)
+            buf = torch.cat([sums, cnt[:, None]], dim=1)
+            self.dist.all_reduce_sum(buf)
+            sums, cnt = buf[:, :-1], buf[:, -1]
+            has = cnt > 0
+            self.centers[has] = sums[has] / cnt[has][:, None]
+            self.counts_out.copy_(cnt.to(torch.int32))
+        self.iteration += 1
+
+    def _assign_torch(self) -> torch.Tensor:
+        out = torch.empty(self.n, dtype=torch.int64, device=self.X.device)
+        Cc = self.centers
+        chunk = max(1, (64 << 20) // max(self.k * 8, 1))
+        if self.X.dtype == torch.float64:
+            for i in range(0, self.n, chunk):                      # exact (x-c)^2 form for parity data
+                x = self.X[i:i + chunk]
+                dmat = ((x[:, None, :] - Cc[None, :, :]) ** 2).sum(-1)
+                out[i:i + chunk] = dmat.argmin(dim=1)
+        else:
+            cn = (Cc * Cc).sum(1)
+            Cm = Cc.to(self.X.dtype)
+            for i in range(0, self.n, chunk):
+                x = self.X[i:i + chunk]
+                dmat = cn[None, :] - 2.0 * (x @ Cm.T).float()
+                out[i:i + chunk] = dmat.argmin(dim=1)
+        return out
+
+    def assign(self) -> torch.Tensor:
+        """Assignment of the local points under the current centres (int64)."""
+        if self.backend == "fused":
+            out = torch.empty(self.n, dtype=torch.int32, device=self.X.device)
+            _native.check(self.lib.dapb_kmeans_assign(self.X.data_ptr(), self.n, self.d, _DT[self.X.dtype],
+                                                      self.centers.data_ptr(), self.k, out.data_ptr(), 0, 0,
+                                                      _native.stream_ptr()), "kmeans_assign")
+            return out.to(torch.int64)
+        return self._assign_torch()

@@ -380,3 +380,92 @@ class ShardedLogisticEngine:
             self.w += self.delta_w
         else:
             self.w.copy_((1 - beta) * self.w + beta * S / self.P)
+
+
+class StreamingLogisticEngine:
+    """End-to-end streaming trainer: every step's mini-batch arrives from *pinned host memory*.
+
+    ``fit_stream(batches)`` uploads batch ``i + 1`` on a copy stream while batch ``i`` runs through the
+    fused step kernel (all rows of the batch are used; the data loader did the sampling), evaluates the
+    updated model on a resident test set -- the reference computes test accuracy every iteration
+    (optimization/ssgd.py:107-112) -- and yields ``(accuracy, global batch size)`` read back to the host.
+    """
+
+    def __init__(self, dim: int, dtype: torch.dtype, max_batch_rows: int, cfg: LogisticConfig,
+                 X_test: torch.Tensor, y_test: torch.Tensor, dist: Optional[Dist] = None, backend: str = "fused"):
+        self.dist = dist or current()
+        dev = self.dist.device
+        self.bufs = [(torch.empty(max_batch_rows, dim, dtype=dtype, device=dev),
+                      torch.empty(max_batch_rows, dtype=torch.float32, device=dev)) for _ in range(2)]
+        gd_like = LogisticConfig(**{**cfg.__dict__})
+        gd_like.mini_batch_fraction = 1.0
+        self.engines = [ShardedLogisticEngine(Xb, yb, gd_like, dist=self.dist, backend=backend) for Xb, yb in self.bufs]
+        self.engines[0].threshold24 = self.engines[1].threshold24 = 1 << 24      # use every uploaded row
+        for e in self.engines:
+            if backend == "fused":
+                e._args.threshold24 = 1 << 24
+        # both engines share one set of weights
+        self.engines[1].w, self.engines[1].w_local, self.engines[1].delta_w = (self.engines[0].w, self.engines[0].w_local,
+                                                                                self.engines[0].delta_w)
+        if backend == "fused":
+            a = self.engines[1]._args
+            a.w, a.w_local, a.delta_w = self.engines[0].w.data_ptr(), self.engines[0].w_local.data_ptr(), self.engines[0].delta_w.data_ptr()
+        self.X_test, self.y_test = X_test, y_test.float()
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.result_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+        self.result_dev = torch.zeros(2, dtype=torch.float32, device=dev)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    @property
+    def w(self):
+        return self.engines[0].w
+
+    def _upload(self, slot: int, Xh: torch.Tensor, yh: torch.Tensor):
+        Xd, yd = self.bufs[slot]
+        n = Xh.shape[0]
+        with torch.cuda.stream(self.copy_stream):
+            Xd[:n].copy_(Xh, non_blocking=True)
+            yd[:n].copy_(yh, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self.copy_stream)
+        self.h2d_bytes += Xh.numel() * Xh.element_size() + yh.numel() * yh.element_size()
+        return n, ev
+
+    def fit_stream(self, batches):
+        it = iter(batches)
+        try:
+            nxt = next(it)
+        except StopIteration:
+            return
+        slot = 0
+        pending = self._upload(slot, *nxt)
+        main = torch.cuda.current_stream()
+        done_compute = [None, None]
+        while pending is not None:
+            n, ev = pending
+            cur = slot
+            try:
+                nxt = next(it)
+                slot ^= 1
+                if done_compute[slot] is not None:
+                    self.copy_stream.wait_event(done_compute[slot])     # buffer free again?
+                pending = self._upload(slot, *nxt)
+            except StopIteration:
+                pending = None
+            main.wait_event(ev)
+            eng = self.engines[cur]
+            eng.n_rows = n
+            if eng.backend == "fused":
+                eng._args.n_rows = n
+            eng.step()
+            acc = eng.evaluate(self.X_test, self.y_test)
+            self.result_dev[0:1].copy_(acc)
+            self.result_dev[1:2].copy_(eng.last_count.float())
+            done = torch.cuda.Event()
+            done.record(main)
+            done_compute[cur] = done
+            self.result_host.copy_(self.result_dev, non_blocking=True)
+            main.synchronize()                                           # the step's result is on the host
+            self.d2h_bytes += 8
+            yield float(self.result_host[0]), int(self.result_host[1])

@@ -1,0 +1,179 @@
+"""PageRank (reference: ``graph_computation/pagerank.py``).
+
+Graph preparation mirrors ``links.distinct().groupByKey()`` (:41): duplicate edges are dropped,
+self-loops kept; ``n`` is the number of distinct SOURCE vertices (:44).  The iteration is the vector
+form of :52-57 including the reference's "absent vertex" rule.
+
+Backends: ``oracle`` (Python floats, bit-exact with the values recorded in pagerank.py:66-68), ``torch``
+(CSR SpMV via ``index_add_`` + ``all_gather`` -- the NCCL baseline), ``fused`` (csrc/pagerank.cu: SpMV +
+damping + all-gather push in one launch per iteration).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, Iterable, Optional, Tuple
+
+import numpy as np
+import torch
+
+from .. import _native
+from ..config import PageRankConfig
+from ..oracle.algorithms import pagerank_oracle
+from ..parallel.dist import Dist, current
+from ..parallel.partition import vertex_range
+
+
+@dataclass
+class ShardedGraph:
+    """dst-range shard of the de-duplicated graph in CSR(A^T) form."""
+    V: int
+    n_sources: int
+    n_edges: int                 # global, after de-duplication
+    v0: int
+    v1: int
+    row_ptr: torch.Tensor        # int64 [nv_local + 1]
+    col_idx: torch.Tensor        # int32 [nnz_local] source ids
+    inv_outdeg: torch.Tensor     # float32 [nv_local]
+    outdeg_local: torch.Tensor   # int64 [nv_local]
+    heavy: Optional[torch.Tensor] = None
+    heavy_threshold: int = 2048
+
+
+def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Optional[Dist] = None,
+                        heavy_threshold: int = 2048) -> ShardedGraph:
+    """De-duplicate (ref pagerank.py:41) and build this rank's CSR(A^T) rows.  ``src``/``dst`` hold the FULL
+    edge list on every rank (the generators are deterministic), int64 on the target device."""
+    dist = dist or current()
+    key = torch.unique(dst.to(torch.int64) * V + src.to(torch.int64))        # sorted by (dst, src)
+    d_all = torch.div(key, V, rounding_mode="floor")
+    s_all = key - d_all * V
+    n_edges = int(key.numel())
+    outdeg = torch.bincount(s_all, minlength=V)
+    n_sources = int((outdeg > 0).sum().item())
+    v0, v1 = vertex_range(V, dist.rank, dist.world)
+    lo = int(torch.searchsorted(d_all, torch.tensor([v0], device=d_all.device)).item())
+    hi = int(torch.searchsorted(d_all, torch.tensor([v1], device=d_all.device)).item())
+    d_loc, s_loc = d_all[lo:hi] - v0, s_all[lo:hi]
+    indeg = torch.bincount(d_loc, minlength=v1 - v0)
+    row_ptr = torch.zeros(v1 - v0 + 1, dtype=torch.int64, device=src.device)
+    row_ptr[1:] = torch.cumsum(indeg, 0)
+    od = outdeg[v0:v1]
+    inv = torch.where(od > 0, 1.0 / od.clamp(min=1).to(torch.float32), torch.zeros((), device=src.device))
+    heavy = torch.nonzero(indeg >= heavy_threshold).squeeze(1).to(torch.int32)
+    if heavy.numel():
+        order = torch.argsort(indeg[heavy.long()], descending=True)
+        heavy = heavy[order].contiguous()
+    return ShardedGraph(V=V, n_sources=n_sources, n_edges=n_edges, v0=v0, v1=v1, row_ptr=row_ptr,
+                        col_idx=s_loc.to(torch.int32).contiguous(), inv_outdeg=inv.contiguous(), outdeg_local=od,
+                        heavy=heavy if heavy.numel() else None, heavy_threshold=heavy_threshold)
+
+
+class ShardedPageRank:
+    """Iterates PageRank on a :class:`ShardedGraph`; ``ranks_local`` holds the owned slice."""
+
+    def __init__(self, graph: ShardedGraph, cfg: PageRankConfig, dist: Optional[Dist] = None,
+                 backend: str = "fused", heap=None, grid: int = 0, dtype=torch.float32):
+        self.g, self.cfg, self.backend = graph, cfg, backend
+        self.dtype = torch.float32 if backend == "fused" else dtype
+        self.dist = dist or current()
+        dev = graph.row_ptr.device
+        self.nv = graph.v1 - graph.v0
+        self.ranks_local = torch.zeros(self.nv, dtype=torch.float32, device=dev)
+        self.n = max(graph.n_sources, 1)
+        self.grid = grid
+        self.it = 0
+        if backend == "fused":
+            from ..parallel.symm import default_heap
+            self.lib = _native.load()
+            self.heap = heap or default_heap(max(64 << 20, 2 * graph.V * 4 + (8 << 20)))
+            self.region = self.heap.region(f"pagerank_V{graph.V}", 2 * graph.V * 4, _native.MAX_RANKS)
+            self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)
+        else:
+            self.c = None
+        self.reset()
+
+    def reset(self):
+        g = self.g
+        self.it = 0
+        r0 = 1.0 / self.n
+        if self.backend == "fused":
+            if self.region.epoch % 2:
+                self.region.epoch += 1            # init writes parity 0 == (epoch_of_first_step - 1) & 1
+            torch.cuda.synchronize()
+            self.dist.barrier()
+            _native.check(self.lib.dapb_pagerank_init(self.heap.comm_ref(), g.inv_outdeg.data_ptr(), self.nv, g.v0, g.V,
+                                                      r0, self.region.payload_off, _native.stream_ptr()), "pagerank_init")
+            torch.cuda.synchronize()
+            self.dist.barrier()
+            self._first = True
+        else:
+            self.inv = torch.where(g.outdeg_local > 0, 1.0 / g.outdeg_local.clamp(min=1).to(self.dtype),
+                                   torch.zeros((), dtype=self.dtype, device=g.row_ptr.device))
+            self.c = self._gather(r0 * self.inv)
+        io = g.inv_outdeg.to(self.dtype)
+        self.ranks_local = torch.where(io > 0, torch.full_like(io, r0), torch.zeros_like(io))
+
+    def _gather(self, loc: torch.Tensor) -> torch.Tensor:
+        if self.dist.world == 1:
+            return loc.clone()
+        sizes = [vertex_range(self.g.V, r, self.dist.world) for r in range(self.dist.world)]
+        m = max(b - a for a, b in sizes)
+        pad = torch.zeros(m, dtype=loc.dtype, device=loc.device)
+        pad[:loc.numel()] = loc
+        parts = self.dist.all_gather(pad)
+        return torch.cat([p[:b - a] for p, (a, b) in zip(parts, sizes)])
+
+    def step(self):
+        g, cfg = self.g, self.cfg
+        base, damp = cfg.q / self.n, 1.0 - cfg.q
+        if self.backend == "fused":
+            heavy = g.heavy
+            _native.check(self.lib.dapb_pagerank_step(
+                self.heap.comm_ref(), g.row_ptr.data_ptr(), g.col_idx.data_ptr(), g.inv_outdeg.data_ptr(),
+                _native.ptr(heavy), 0 if heavy is None else heavy.numel(), g.heavy_threshold, self.nv, g.v0, g.V,
+                base, damp, self.ranks_local.data_ptr(), self.region.payload_off, self.region.flag_base,
+                self.region.next_epoch(), self.ticket.data_ptr(), 0 if self._first else 1, self.grid,
+                _native.stream_ptr()), "pagerank_step")
+            self._first = False
+        else:
+            vals = self.c[g.col_idx.long()]
+            rows = torch.repeat_interleave(torch.arange(self.nv, device=vals.device), g.row_ptr[1:] - g.row_ptr[:-1])
+            s = torch.zeros(self.nv, dtype=self.dtype, device=vals.device)
+            s.index_add_(0, rows, vals)
+            r = torch.where(s > 0, base + damp * s, torch.zeros_like(s))
+            self.ranks_local = r
+            self.c = self._gather(r * self.inv)
+        self.it += 1
+
+    def finish(self):
+        """Make sure every rank's last pushes landed before buffers are reused (fused backend)."""
+        if self.backend == "fused":
+            torch.cuda.synchronize()
+            self.dist.barrier()
+
+    def ranks(self) -> torch.Tensor:
+        """Full rank vector on every rank (the reference's ``ranks.collect()``, pagerank.py:60)."""
+        self.finish()
+        return self._gather(self.ranks_local)
+
+
+def run_pagerank(edges: Iterable[Tuple[int, int]], cfg: PageRankConfig, backend: str = "auto",
+                 dist: Optional[Dist] = None) -> Dict[int, float]:
+    """Rank the vertices of an edge list with arbitrary integer ids; returns {vertex: rank} for the
+    vertices the reference would print (those that still hold a rank)."""
+    if backend == "auto":
+        backend = "fused" if _native.available() else "torch"
+    edges = [(int(a), int(b)) for a, b in edges]
+    if backend == "oracle":
+        return pagerank_oracle(edges, cfg)
+    dist = dist or current()
+    ids = sorted(set(v for e in edges for v in e))
+    remap = {v: i for i, v in enumerate(ids)}
+    src = torch.tensor([remap[a] for a, _ in edges], dtype=torch.int64, device=dist.device)
+    dst = torch.tensor([remap[b] for _, b in edges], dtype=torch.int64, device=dist.device)
+    g = build_sharded_graph(src, dst, len(ids), dist)
+    pr = ShardedPageRank(g, cfg, dist, backend="fused" if backend == "fused" else "nccl", dtype=torch.float64)
+    for _ in range(cfg.n_iterations):
+        pr.step()
+    r = pr.ranks().double().cpu().numpy()
+    return {ids[i]: float(r[i]) for i in range(len(ids)) if r[i] > 0}

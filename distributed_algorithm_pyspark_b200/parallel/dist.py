@@ -63,6 +63,9 @@ class Dist:
         """Variable-size all-to-all of 1-D/2-D tensors (sizes exchanged first)."""
         if self.world == 1:
             return [send[0]]
+        if self.device.type != "cuda":          # gloo has no all_to_all: exchange through object gather
+            objs = self.all_gather_object([t.cpu().numpy() for t in send])
+            return [torch.from_numpy(objs[r][self.rank]).to(send[0].device) for r in range(self.world)]
         sizes = torch.tensor([s.shape[0] for s in send], dtype=torch.int64, device=send[0].device)
         rsizes = torch.empty_like(sizes)
         dist.all_to_all_single(rsizes, sizes)

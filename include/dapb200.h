@@ -141,6 +141,61 @@ DAPB_API int dapb_lr_eval(const void* X, const float* y, int64_t n_rows, int32_t
  * count_io (device uint64) is atomically incremented. */
 DAPB_API int dapb_mc_pi(uint64_t first, uint64_t n, uint64_t seed, unsigned long long* count_io, void* stream);
 
+/* ------------------------------------------------------------------ F3 k-means ------------
+ * ref: machine_learning/k-means.py:20-28,57-71.  dtype: 0 fp32, 1 bf16, 2 fp64 points; centres and
+ * sums are float (dtype 0/1) or double (dtype 2).  Ties -> lowest index; sums/counts accumulate
+ * atomically (zero them first); assign may be NULL. */
+DAPB_API int dapb_kmeans_assign(const void* X, int64_t n, int32_t d, int32_t dtype, const void* centers,
+                                int32_t k, int32_t* assign, void* sums, int32_t* counts, void* stream);
+/* Fused reduce-scatter(sum,count) -> mean (empty cluster keeps its centre, ref :70-71) -> all-gather. */
+DAPB_API int dapb_kmeans_finalize(const DapbComm* comm, void* sums, int32_t* counts, void* centers, int32_t k,
+                                  int32_t d, int32_t f64, uint64_t payload_off, uint32_t flag_base,
+                                  uint64_t epoch, int32_t* counts_out, int32_t clear_partials, void* stream);
+DAPB_API uint64_t dapb_kmeans_payload_bytes(int32_t world, int32_t k, int32_t d, int32_t elem_bytes);
+
+/* ------------------------------------------------------------------ F4 PageRank -----------
+ * ref: graph_computation/pagerank.py:21-25,44-57.  Contribution vector [2][V] float lives in the
+ * symmetric heap at c_off; iteration `epoch` reads parity (epoch-1)&1 and pushes into parity epoch&1
+ * on every rank.  Host must barrier between dapb_pagerank_init and the first step (wait_prev = 0). */
+DAPB_API int dapb_pagerank_init(const DapbComm* comm, const float* inv_outdeg, int64_t nv_local, int64_t v0,
+                                int64_t V, float r0, uint64_t c_off, void* stream);
+DAPB_API int dapb_pagerank_step(const DapbComm* comm, const int64_t* row_ptr, const int32_t* col_idx,
+                                const float* inv_outdeg, const int32_t* heavy, int32_t n_heavy,
+                                int32_t heavy_threshold, int64_t nv_local, int64_t v0, int64_t V, float base,
+                                float damp, float* ranks_local, uint64_t c_off, uint32_t flag_base,
+                                uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t grid, void* stream);
+
+/* ------------------------------------------------------------------ F6 transitive closure --
+ * ref: graph_computation/transitive_closure.py:27-40.  Pairs are packed (x << 32 | z); the hash set
+ * is open-addressing with 0xFFFF...F as the empty marker (memset 0xFF) and a power-of-two capacity
+ * the caller keeps at load factor <= 0.5.  counters: [0] next-frontier size, [1 + r] per-owner tails. */
+DAPB_API int dapb_tc_seed(const unsigned long long* keys, int64_t n, unsigned long long* table, uint64_t capacity,
+                          unsigned long long* out, unsigned long long* out_count, int32_t world, int32_t rank,
+                          void* stream);
+DAPB_API int dapb_tc_expand(const DapbComm* comm, const int64_t* in_ptr, const int32_t* in_src,
+                            const unsigned long long* frontier, int64_t n_frontier, unsigned long long* table,
+                            uint64_t capacity, unsigned long long* next_frontier, unsigned long long* counters,
+                            uint64_t q_off, uint64_t q_cap, void* stream);
+DAPB_API int dapb_tc_exchange(const DapbComm* comm, unsigned long long* counters, uint64_t q_off, uint64_t q_cap,
+                              uint32_t flag_base, uint64_t epoch, void* stream);
+DAPB_API int dapb_tc_drain(const DapbComm* comm, unsigned long long* table, uint64_t capacity,
+                           unsigned long long* next_frontier, unsigned long long* counters, uint64_t q_off,
+                           uint64_t q_cap, void* stream);
+
+/* ------------------------------------------------------------------ F5 Gram / ALS ----------
+ * ref: matrix_computation/matrix_decomposition.py:19-33,51-67.  dtype: 0 fp32, 1 bf16, 2 fp64. */
+DAPB_API int dapb_gram(const DapbComm* comm, const void* X, const void* Y, int64_t n, int32_t P, int32_t Q,
+                       int64_t ldx, int64_t ldy, int32_t dtype, void* partial, int32_t splits, void* C,
+                       uint32_t* ticket, uint64_t payload_off, uint32_t flag_base, uint64_t epoch,
+                       int32_t do_allreduce, void* stream);
+DAPB_API int dapb_rows_times_small(const void* R, const void* V, int64_t m, int32_t n, int32_t k, int64_t ldr,
+                                   int32_t transpose_r, int32_t f64, void* out, void* stream);
+DAPB_API int dapb_solve_rows(const void* G, double ridge, const void* B, int64_t m, int32_t k, int32_t f64,
+                             void* X, void* stream);
+DAPB_API int dapb_sq_residual(const void* R, const void* U, const void* V, int64_t m, int32_t n, int32_t k,
+                              int32_t f64, double* out, void* stream);
+DAPB_API int dapb_cholesky(void* A, int32_t n, int32_t f64, int32_t* info, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

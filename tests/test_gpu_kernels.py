@@ -1,0 +1,329 @@
+"""Numerics of every native sm_100a kernel against plain PyTorch fp32/fp64 restatements of the same op
+(and against the NumPy oracle where the op is a whole algorithm).  Needs a GPU."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from distributed_algorithm_pyspark_b200 import _native
+from distributed_algorithm_pyspark_b200.config import (ALSConfig, KMeansConfig, LogisticConfig, MonteCarloConfig,
+                                                        PageRankConfig)
+from distributed_algorithm_pyspark_b200.data.datasets import (KMEANS_TOY, PAGERANK_TOY, TC_TOY, rmat_edges_np,
+                                                               synthetic_clusters_np)
+from distributed_algorithm_pyspark_b200.oracle.algorithms import (LogisticInit, als_draw, als_oracle, kmeans_oracle,
+                                                                   logistic_oracle, pagerank_oracle,
+                                                                   transitive_closure_oracle)
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return _native.load()
+
+
+@pytest.fixture(scope="module")
+def heap(dist):
+    from distributed_algorithm_pyspark_b200.parallel.symm import default_heap
+    return default_heap()
+
+
+def test_library_is_native_sm100(lib):
+    sms, maj, mnr, mem = C.c_int32(), C.c_int32(), C.c_int32(), C.c_uint64()
+    _native.check(lib.dapb_device_info(C.byref(sms), C.byref(maj), C.byref(mnr), C.byref(mem)))
+    assert maj.value == 10 and sms.value >= 100 and lib.dapb_version() >= 100
+
+
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+def test_comm_protocol_selftest(lib, world):
+    """F8 flag/epoch protocol with `world` CTAs of one cooperative launch acting as ranks."""
+    n, iters, heap_bytes = 1025, 200, 65536 + 2 * 8 * 1028 * 4 + 4096
+    heaps = torch.zeros(world * heap_bytes, dtype=torch.uint8, device=DEV)
+    fail = torch.zeros(1, dtype=torch.int32, device=DEV)
+    _native.check(lib.dapb_comm_selftest(heaps.data_ptr(), heap_bytes, world, n, iters, fail.data_ptr(), _native.stream_ptr()))
+    torch.cuda.synchronize()
+    assert int(fail.item()) == 0
+
+
+def test_standalone_allreduce_world1(lib, heap):
+    src = torch.randn(1000, device=DEV)
+    dst = torch.zeros_like(src)
+    reg = heap.region("test_ar", 2 * 8 * 1000 * 4, 8)
+    _native.check(lib.dapb_allreduce_f32(heap.comm_ref(), reg.payload_off, reg.flag_base, reg.next_epoch(),
+                                         src.data_ptr(), dst.data_ptr(), 1000, _native.stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.equal(src, dst)
+
+
+# ------------------------------------------------------------------------------------------ F1/F2 parity kernel
+@pytest.mark.parametrize("algo", ["ssgd", "gd", "ma", "bmuf", "easgd"])
+def test_lr_parity_kernel_matches_oracle(breast_cancer, dist, algo):
+    from distributed_algorithm_pyspark_b200.models.logistic import run_logistic
+    d = breast_cancer
+    cfg = LogisticConfig.for_algo(algo, n_iterations=60, seed=0)
+    init = LogisticInit.draw(algo, d.dim, cfg.n_slices, 0)
+    ref = logistic_oracle(d.matrix, d.X_test_aug, d.y_test, cfg, init)
+    got = run_logistic(d, cfg, init, backend="fused", dist=dist)
+    np.testing.assert_allclose(got.w, ref.w, rtol=1e-7, atol=1e-9)
+    assert got.batch_sizes == ref.batch_sizes
+    assert got.accs == pytest.approx(ref.accs, abs=1e-12)
+
+
+def test_lr_parity_full_default_ssgd(breast_cancer, dist):
+    """The reference's default SSGD run (1500 iterations) in one kernel launch."""
+    from distributed_algorithm_pyspark_b200.models.logistic import run_logistic
+    d = breast_cancer
+    cfg = LogisticConfig.for_algo("ssgd", seed=0)
+    init = LogisticInit.draw("ssgd", d.dim, cfg.n_slices, 0)
+    ref = logistic_oracle(d.matrix, d.X_test_aug, d.y_test, cfg, init)
+    got = run_logistic(d, cfg, init, backend="fused", dist=dist)
+    np.testing.assert_allclose(got.w, ref.w, rtol=1e-5, atol=1e-7)
+    assert np.mean(np.array(got.accs) == np.array(ref.accs)) > 0.99
+
+
+# ------------------------------------------------------------------------------------------ F1/F2 step kernel
+def _torch_grad(X, y, w, keep, eps):
+    Xf = X.float()
+    z = Xf @ w
+    r = (1.0 / (torch.exp(-z) + 1.0 + eps) - y) * keep.float()
+    return r @ Xf, int(keep.sum().item())
+
+
+@pytest.mark.parametrize("dtype,D,n", [(torch.bfloat16, 1024, 20000), (torch.bfloat16, 256, 5000), (torch.float32, 1024, 7001),
+                                        (torch.float32, 128, 3000), (torch.float32, 31, 999), (torch.bfloat16, 40, 515)])
+def test_lr_step_gradient_vs_torch(dist, dtype, D, n):
+    from distributed_algorithm_pyspark_b200.models.logistic import ShardedLogisticEngine
+    from distributed_algorithm_pyspark_b200.utils.philox import philox_row_mask_torch
+    torch.manual_seed(0)
+    X = (torch.randn(n, D, device=DEV) * 0.5).to(dtype).contiguous()
+    y = (torch.rand(n, device=DEV) < 0.5).float()
+    cfg = LogisticConfig.for_algo("ssgd", mini_batch_fraction=0.1, sample_seed=42, seed=1)
+    eng = ShardedLogisticEngine(X, y, cfg, row_base=1000, dist=dist, backend="fused")
+    w0 = torch.randn(D, device=DEV) * 0.05
+    eng.w.copy_(w0)
+    for it in (0, 3):
+        eng._launch(_native.FIN_GRAD_ONLY, eng.w, it)
+        torch.cuda.synchronize()
+        keep = philox_row_mask_torch(n, 0.1, 42, it, 1000, device=DEV)
+        g_ref, cnt_ref = _torch_grad(X, y, w0, keep, 0.0)
+        assert int(eng.last_count.item()) == cnt_ref
+        np.testing.assert_allclose(eng.g.cpu().numpy(), g_ref.cpu().numpy(), rtol=2e-3, atol=2e-3 * float(g_ref.abs().max()))
+
+
+def test_lr_step_explicit_mask_and_all_rows(dist):
+    from distributed_algorithm_pyspark_b200.models.logistic import ShardedLogisticEngine
+    torch.manual_seed(1)
+    n, D = 4096, 512
+    X = torch.randn(n, D, device=DEV).to(torch.bfloat16)
+    y = (torch.rand(n, device=DEV) < 0.3).float()
+    eng = ShardedLogisticEngine(X, y, LogisticConfig.for_algo("gd"), dist=dist, backend="fused")
+    w0 = eng.w.clone()
+    eng._launch(_native.FIN_GRAD_ONLY, eng.w, 0)
+    g_ref, cnt = _torch_grad(X, y, w0, torch.ones(n, device=DEV, dtype=torch.bool), 0.0)
+    torch.cuda.synchronize()
+    assert int(eng.last_count.item()) == n
+    np.testing.assert_allclose(eng.g.cpu().numpy(), g_ref.cpu().numpy(), rtol=2e-3, atol=2e-3 * float(g_ref.abs().max()))
+    mask = (torch.rand(n, device=DEV) < 0.2).to(torch.uint8)
+    eng._args.mask = mask.data_ptr()
+    eng._launch(_native.FIN_GRAD_ONLY, eng.w, 0)
+    g_ref, cnt = _torch_grad(X, y, w0, mask.bool(), 0.0)
+    torch.cuda.synchronize()
+    assert int(eng.last_count.item()) == cnt
+    np.testing.assert_allclose(eng.g.cpu().numpy(), g_ref.cpu().numpy(), rtol=2e-3, atol=2e-3 * float(g_ref.abs().max()))
+
+
+@pytest.mark.parametrize("algo", ["ssgd", "gd", "ma", "bmuf", "easgd"])
+def test_lr_engine_fused_matches_torch_baseline(dist, algo):
+    """Fused step (sample+fwd+bwd+reduce+update in one launch) vs the torch.matmul baseline, same Philox masks."""
+    from distributed_algorithm_pyspark_b200.models.logistic import ShardedLogisticEngine
+    torch.manual_seed(2)
+    n, D = 30000, 256
+    X = (torch.randn(n, D, device=DEV) * 0.3).float().contiguous()
+    X[:, -1] = 1
+    wstar = torch.randn(D, device=DEV) * 0.2
+    y = (torch.rand(n, device=DEV) < torch.sigmoid(X @ wstar)).float()
+    cfg = LogisticConfig.for_algo(algo, eta=0.05 if algo != "gd" else 1e-5, mini_batch_fraction=0.1, seed=3)
+    a = ShardedLogisticEngine(X, y, cfg, dist=dist, backend="fused")
+    b = ShardedLogisticEngine(X, y, cfg, dist=dist, backend="nccl")
+    for _ in range(6):
+        a.step()
+        b.step()
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(a.w.cpu().numpy(), b.w.cpu().numpy(), rtol=2e-3, atol=2e-5)
+    acc_a = float(a.evaluate(X[:5000], y[:5000]).item())
+    acc_b = float(b.evaluate(X[:5000], y[:5000]).item())
+    assert abs(acc_a - acc_b) < 2e-3 and acc_a > 0.5
+
+
+# ------------------------------------------------------------------------------------------ F7
+def test_monte_carlo_exact_vs_host_twin(lib, dist):
+    from distributed_algorithm_pyspark_b200.models.monte_carlo import accept_count_np, run_monte_carlo
+    for first, n, seed in [(0, 100001, 7), (12345, 77777, (1 << 35) + 9), (1, 2, 3)]:
+        cnt = torch.zeros(1, dtype=torch.int64, device=DEV)
+        _native.check(lib.dapb_mc_pi(first, n, seed, cnt.data_ptr(), _native.stream_ptr()))
+        assert int(cnt.item()) == accept_count_np(first, n, seed)
+    pi, count = run_monte_carlo(MonteCarloConfig(n=4_000_000, seed=1), backend="fused", dist=dist)
+    assert abs(pi - np.pi) < 4 * 4 * np.sqrt((np.pi / 4) * (1 - np.pi / 4) / 4e6)
+
+
+# ------------------------------------------------------------------------------------------ F3
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float64])
+def test_kmeans_assign_simple_vs_torch(lib, dtype):
+    torch.manual_seed(0)
+    n, d, k = 5000, 24, 37
+    X = torch.randn(n, d, device=DEV).to(dtype).contiguous()
+    acc = torch.float64 if dtype == torch.float64 else torch.float32
+    Cc = torch.randn(k, d, device=DEV).to(acc).contiguous()
+    assign = torch.empty(n, dtype=torch.int32, device=DEV)
+    sums = torch.zeros(k, d, dtype=acc, device=DEV)
+    counts = torch.zeros(k, dtype=torch.int32, device=DEV)
+    dt = {torch.float32: 0, torch.bfloat16: 1, torch.float64: 2}[dtype]
+    _native.check(lib.dapb_kmeans_assign(X.data_ptr(), n, d, dt, Cc.data_ptr(), k, assign.data_ptr(), sums.data_ptr(),
+                                         counts.data_ptr(), _native.stream_ptr()))
+    dm = ((X.to(acc)[:, None, :] - Cc[None]) ** 2).sum(-1)
+    ref = dm.argmin(1)
+    got = assign.long()
+    mism = got != ref
+    if mism.any():      # only genuine near-ties may differ
+        gap = (dm.gather(1, got[:, None]) - dm.gather(1, ref[:, None])).abs().squeeze(1)[mism]
+        assert float(gap.max()) < 1e-4
+    ref_s = torch.zeros_like(sums).index_add_(0, got, X.to(acc))
+    np.testing.assert_allclose(sums.cpu().numpy(), ref_s.cpu().numpy(), rtol=1e-4, atol=1e-3)
+    assert torch.equal(counts.long(), torch.bincount(got, minlength=k))
+
+
+def test_kmeans_fused_toy_and_synthetic_match_oracle(dist):
+    from distributed_algorithm_pyspark_b200.models.kmeans import run_kmeans
+    res = run_kmeans(KMEANS_TOY, KMeansConfig(), backend="fused", dist=dist)
+    np.testing.assert_array_equal(res.centers, [[10, 2], [1, 2]])
+    pts, _ = synthetic_clusters_np(3000, 6, 5, seed=3)
+    cfg = KMeansConfig(k=5, n_slices=4, n_iterations=6)
+    ref = kmeans_oracle(pts, cfg)
+    got = run_kmeans(pts, cfg, backend="fused", dist=dist)
+    np.testing.assert_allclose(got.centers, ref.centers, rtol=1e-9)
+    assert (got.assignment == ref.assignment).all()
+
+
+def test_kmeans_empty_cluster_and_tie(dist):
+    from distributed_algorithm_pyspark_b200.models.kmeans import run_kmeans
+    pts = np.array([[0.0, 0.0], [2.0, 0.0]])
+    init = np.array([[1.0, 0.0], [1.0, 0.0], [50.0, 50.0]])
+    res = run_kmeans(pts, KMeansConfig(k=3, n_iterations=2), backend="fused", dist=dist, init_centers=init)
+    np.testing.assert_array_equal(res.centers[2], [50.0, 50.0])
+    np.testing.assert_array_equal(res.assignment, [0, 0])
+
+
+# ------------------------------------------------------------------------------------------ F4
+def test_pagerank_fused_toy_and_random_vs_oracle(dist):
+    from distributed_algorithm_pyspark_b200.models.pagerank import run_pagerank
+    got = run_pagerank(PAGERANK_TOY, PageRankConfig(), backend="fused", dist=dist)
+    ref = pagerank_oracle(PAGERANK_TOY, PageRankConfig())
+    assert set(got) == set(ref) and max(abs(got[k] - ref[k]) for k in ref) < 1e-6
+    s, d = rmat_edges_np(10, 8, seed=1)
+    e = list(zip(s.tolist(), d.tolist()))
+    ref = pagerank_oracle(e, PageRankConfig(n_iterations=8))
+    got = run_pagerank(e, PageRankConfig(n_iterations=8), backend="fused", dist=dist)
+    assert set(got) == set(ref)
+    assert max(abs(got[k] - ref[k]) / ref[k] for k in ref) < 1e-4
+
+
+def test_pagerank_heavy_row_path(dist):
+    from distributed_algorithm_pyspark_b200.models.pagerank import ShardedPageRank, build_sharded_graph
+    s, d = rmat_edges_np(11, 16, seed=2)
+    src, dst = torch.as_tensor(s, device=DEV), torch.as_tensor(d, device=DEV)
+    V = 1 << 11
+    cfg = PageRankConfig(n_iterations=5)
+    outs = []
+    for thr in (1 << 30, 16):             # no heavy rows vs many heavy rows
+        g = build_sharded_graph(src, dst, V, dist, heavy_threshold=thr)
+        pr = ShardedPageRank(g, cfg, dist, backend="fused")
+        for _ in range(cfg.n_iterations):
+            pr.step()
+        outs.append(pr.ranks().cpu().numpy())
+    base = ShardedPageRank(build_sharded_graph(src, dst, V, dist), cfg, dist, backend="nccl")
+    for _ in range(cfg.n_iterations):
+        base.step()
+    np.testing.assert_allclose(outs[0], outs[1], rtol=1e-5, atol=1e-9)
+    np.testing.assert_allclose(outs[0], base.ranks().cpu().numpy(), rtol=1e-4, atol=1e-9)
+
+
+# ------------------------------------------------------------------------------------------ F6
+def test_transitive_closure_fused_vs_oracle(dist):
+    from distributed_algorithm_pyspark_b200.models.transitive_closure import run_transitive_closure
+    r = run_transitive_closure(TC_TOY, backend="fused", dist=dist)
+    assert r.n_pairs == 9 and r.rounds == 3
+    rs = np.random.RandomState(4)
+    e = list(zip(rs.randint(0, 300, 500).tolist(), rs.randint(0, 300, 500).tolist()))
+    n, rounds, pairs = transitive_closure_oracle(e)
+    got = run_transitive_closure(e, backend="fused", dist=dist)
+    assert got.n_pairs == n and got.rounds == rounds
+    assert sorted(map(tuple, got.pairs.tolist())) == sorted(pairs)
+
+
+# ------------------------------------------------------------------------------------------ F5
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2), (torch.float64, 1e-11)])
+def test_gram_vs_torch(dist, dtype, tol):
+    from distributed_algorithm_pyspark_b200.models.matrix_decomposition import GramOp
+    torch.manual_seed(0)
+    n, P, Q = 3001, 70, 45
+    X = torch.randn(n, P, device=DEV).to(dtype)
+    Y = torch.randn(n, Q, device=DEV).to(dtype)
+    op = GramOp(P, Q, dtype, DEV, dist, tag="t")
+    got = op(X, Y).double().cpu().numpy()
+    ref = (X.double().T @ Y.double()).cpu().numpy()
+    np.testing.assert_allclose(got, ref, rtol=tol, atol=tol * np.abs(ref).max())
+
+
+def test_solve_rows_and_cholesky_vs_torch(lib):
+    torch.manual_seed(0)
+    for k, dt in [(10, torch.float64), (33, torch.float32)]:
+        A = torch.randn(200, k, device=DEV, dtype=dt)
+        G = (A.T @ A).contiguous()
+        B = torch.randn(57, k, device=DEV, dtype=dt)
+        Xo = torch.empty_like(B)
+        _native.check(lib.dapb_solve_rows(G.data_ptr(), 0.5, B.data_ptr(), 57, k, int(dt == torch.float64), Xo.data_ptr(),
+                                          _native.stream_ptr()))
+        ref = torch.linalg.solve(G + 0.5 * torch.eye(k, device=DEV, dtype=dt), B.T).T
+        np.testing.assert_allclose(Xo.cpu().numpy(), ref.cpu().numpy(), rtol=1e-3 if dt == torch.float32 else 1e-9,
+                                   atol=1e-4 if dt == torch.float32 else 1e-11)
+    n = 96
+    A = torch.randn(400, n, device=DEV, dtype=torch.float64)
+    G = (A.T @ A).contiguous()
+    L = G.clone()
+    info = torch.zeros(1, dtype=torch.int32, device=DEV)
+    _native.check(lib.dapb_cholesky(L.data_ptr(), n, 1, info.data_ptr(), _native.stream_ptr()))
+    assert int(info.item()) == 0
+    np.testing.assert_allclose(L.cpu().numpy(), torch.linalg.cholesky(G).cpu().numpy(), rtol=1e-9, atol=1e-9)
+
+
+def test_als_fused_matches_oracle(dist):
+    from distributed_algorithm_pyspark_b200.models.matrix_decomposition import run_als
+    cfg = ALSConfig(seed=0)
+    R, U, V = als_draw(cfg)
+    _, _, errs = als_oracle(R, U, V, cfg)
+    got = run_als(cfg, backend="fused", dist=dist)
+    np.testing.assert_allclose(got.rmse, errs, rtol=1e-7)
+
+
+# ------------------------------------------------------------------------------------------ entry scripts
+def test_entry_scripts_run_fused(tmp_path):
+    import subprocess, sys, os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    checks = {
+        "graph_computation/pagerank.py": "1 has rank: 0.3889",
+        "graph_computation/transitive_closure.py": "The original graph has 9 paths",
+        "machine_learning/k-means.py": "Final centers: [array([10.,  2.]), array([1., 2.])]",
+        "randomized_algorithm/monte_carlo.py": "Pi is roughly 3.1",
+        "matrix_computation/matrix_decomposition.py": "iterations: 4, rmse: 0.0314",
+    }
+    for script, needle in checks.items():
+        out = subprocess.run([sys.executable, os.path.join(root, script), "--backend", "fused", "--seed", "0",
+                              "--out-dir", str(tmp_path)], capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, out.stderr[-2000:]
+        assert needle in out.stdout, out.stdout[-500:]
+    out = subprocess.run([sys.executable, os.path.join(root, "optimization/ssgd.py"), "--backend", "fused", "--seed", "0",
+                          "--out-dir", str(tmp_path), "--quiet"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "Final acc: " in out.stdout and "Initial w: " in out.stdout
