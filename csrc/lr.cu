@@ -13,6 +13,8 @@
 //    last CTA performs the cross-GPU all-reduce over peer memory and the optimiser update).
 #include <cooperative_groups.h>
 
+#include <mutex>
+
 #include "comm.cuh"
 #include "philox.cuh"
 
@@ -615,3 +617,96 @@ extern "C" int dapb_lr_eval(const void* X, const float* y, int64_t n_rows, int32
   DAPB_LAUNCH_CHECK();
   return 0;
 }
+
+// =================================================================================================
+// Allocation-free gradient entry point
+// =================================================================================================
+// Some users of this library are not in a position to allocate device memory: a host process whose
+// own allocator has already reserved the whole GPU for the resident data shard (the 64 GiB shards of
+// the benchmark configuration leave no room to negotiate), a serving / control loop that must not hit
+// the device-wide synchronisation that cudaMalloc and cudaFree imply, or a plug-in callback that is
+// simply forbidden from calling allocating CUDA APIs.  For them the mini-batch gradient is offered
+// once more with NO caller-provided scratch: the per-CTA partial sums, per-CTA counts and the
+// last-CTA ticket of the step kernel live in the file-scope device array below.
+//
+// Cost and limits: the array occupies kNoAllocScratchBytes (about 1.16 MiB) on EVERY GPU that loads
+// this library, from load until the process exits.  It is sized for D <= DAPB_NOALLOC_MAX_D features
+// and a grid of at most DAPB_NOALLOC_MAX_GRID CTAs; larger requests are refused.  All calls share it
+// and it keeps whatever the previous call left behind, so the ticket word is cleared on the stream
+// before each launch (partials and counts are fully rewritten by every launch before they are read).
+// Two calls whose kernels can overlap on the GPU (different streams, or different host threads on the
+// same device) race on the array -- serialise them.
+namespace {
+
+constexpr size_t kNoAllocTicketBytes = 256;
+constexpr size_t kNoAllocCountsBytes = ((size_t)DAPB_NOALLOC_MAX_GRID * sizeof(int32_t) + 255) / 256 * 256;
+constexpr size_t kNoAllocPartialBytes = (size_t)DAPB_NOALLOC_MAX_GRID * DAPB_NOALLOC_MAX_D * sizeof(float);
+constexpr size_t kNoAllocScratchBytes = kNoAllocTicketBytes + kNoAllocCountsBytes + kNoAllocPartialBytes;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+// In host code `g_noalloc_scratch` is only a stand-in symbol, not a device address; the real
+// address is looked up once per device (with that device current) and cached here.
+constexpr int kMaxDevices = 64;
+static unsigned char* g_noalloc_dev_ptr[kMaxDevices] = {nullptr};
+static int g_noalloc_grid[kMaxDevices] = {0};
+
+static std::mutex g_noalloc_mutex;
+
+int noalloc_setup(int dev, unsigned char** out, int* grid_out) {
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (g_noalloc_dev_ptr[dev] == nullptr) {
+    unsigned char* p = nullptr;
+    DAPB_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+    int sms = 0;
+    DAPB_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    int grid = 2 * sms;
+    if (grid > DAPB_NOALLOC_MAX_GRID) grid = DAPB_NOALLOC_MAX_GRID;
+    g_noalloc_grid[dev] = grid;
+    g_noalloc_dev_ptr[dev] = p;
+  }
+  *out = g_noalloc_dev_ptr[dev];
+  *grid_out = g_noalloc_grid[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int dapb_lr_grad_noalloc(const void* X, const float* y, int64_t n_rows, int64_t row_base, int32_t D,
+                                    int32_t dtype, const uint8_t* mask, uint64_t seed, uint32_t iteration,
+                                    uint32_t threshold24, float eps, const float* w, float* g_out,
+                                    int32_t* cnt_out, void* stream) {
+  DAPB_REQUIRE(X && y && w && g_out && cnt_out, "lr_grad_noalloc: null argument");
+  DAPB_REQUIRE(dtype == 0 || dtype == 1, "lr_grad_noalloc: dtype must be 0 (fp32) or 1 (bf16)");
+  DAPB_REQUIRE(n_rows >= 0, "lr_grad_noalloc: negative row count");
+  DAPB_REQUIRE(D >= 1 && D <= DAPB_NOALLOC_MAX_D,
+               "lr_grad_noalloc: D=%d is outside [1, %d], the size the built-in scratch array was compiled for; "
+               "use dapb_lr_step with caller-provided scratch instead", D, DAPB_NOALLOC_MAX_D);
+  int dev = 0;
+  DAPB_CUDA_CHECK(cudaGetDevice(&dev));
+  DAPB_REQUIRE(dev >= 0 && dev < kMaxDevices, "lr_grad_noalloc: device ordinal %d not supported", dev);
+  unsigned char* base = nullptr;
+  int grid = 0;
+  int rc = noalloc_setup(dev, &base, &grid);      // first call on a device: one cudaGetSymbolAddress
+  if (rc != 0) return rc;
+
+  DapbLrStepArgs a;
+  memset(&a, 0, sizeof(a));
+  a.X = X; a.y = y; a.n_rows = n_rows; a.row_base = row_base; a.D = D; a.dtype = dtype;
+  a.mask = mask; a.seed = seed; a.iteration = iteration; a.threshold24 = threshold24; a.eps = eps;
+  a.w_fwd = w;
+  a.ticket = reinterpret_cast<uint32_t*>(base);
+  a.counts = reinterpret_cast<int32_t*>(base + kNoAllocTicketBytes);
+  a.partials = reinterpret_cast<float*>(base + kNoAllocTicketBytes + kNoAllocCountsBytes);
+  a.grid = grid;
+  a.fin = DAPB_LR_FIN_GRAD_ONLY;
+  a.g_out = g_out; a.cnt_out = cnt_out;
+  DapbComm c;
+  memset(&c, 0, sizeof(c));
+  c.world = 1;
+  // the array keeps the previous call's contents: the ticket must start at zero
+  DAPB_CUDA_CHECK(cudaMemsetAsync(a.ticket, 0, sizeof(uint32_t), (cudaStream_t)stream));
+  return dapb_lr_step(&a, &c, stream);
+}
+
+extern "C" uint64_t dapb_lr_grad_noalloc_scratch_bytes(void) { return (uint64_t)kNoAllocScratchBytes; }

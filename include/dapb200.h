@@ -135,6 +135,25 @@ DAPB_API int dapb_lr_step(const DapbLrStepArgs* args, const DapbComm* comm, void
 DAPB_API int dapb_lr_eval(const void* X, const float* y, int64_t n_rows, int32_t D, int32_t dtype,
                  const float* w, float eps, float* acc_out, uint32_t* scratch2, void* stream);
 
+/* Mini-batch gradient WITHOUT any caller-provided scratch and without a single allocation inside.
+ * (No counterpart in the reference -- it exists for hosts that cannot allocate device memory: a process
+ * whose own allocator already owns the whole GPU, a latency-critical loop that must avoid the device-wide
+ * synchronisation of cudaMalloc/cudaFree, or a plug-in hook that may not call allocating CUDA APIs.)
+ * Same math and same kernels as dapb_lr_step(fin = DAPB_LR_FIN_GRAD_ONLY): g_out[D] receives
+ * sum over kept rows of (sigmoid(x.w) - y) x, cnt_out[1] the number of kept rows.  The grid-reduction
+ * scratch is a built-in device array of dapb_lr_grad_noalloc_scratch_bytes() (~1.16 MiB) that every GPU
+ * loading this library holds until exit.  Limits: 1 <= D <= DAPB_NOALLOC_MAX_D, otherwise DAPB_ERR_INVALID
+ * with a message.  The first call on each device looks the array's address up (cudaGetSymbolAddress);
+ * make that first call outside of any stream capture.  All calls share the array: calls that may overlap
+ * on the GPU (other streams / threads) race -- serialise them. */
+#define DAPB_NOALLOC_MAX_D 1024
+#define DAPB_NOALLOC_MAX_GRID 296
+DAPB_API int dapb_lr_grad_noalloc(const void* X, const float* y, int64_t n_rows, int64_t row_base, int32_t D,
+                                  int32_t dtype, const uint8_t* mask, uint64_t seed, uint32_t iteration,
+                                  uint32_t threshold24, float eps, const float* w, float* g_out,
+                                  int32_t* cnt_out, void* stream);
+DAPB_API uint64_t dapb_lr_grad_noalloc_scratch_bytes(void);
+
 /* ------------------------------------------------------------------ F7 Monte-Carlo pi ----
  * ref: randomized_algorithm/monte_carlo.py:17-31.  Sample i in [first, first+n) comes from
  * Philox counter i/2; a point is accepted iff x^2+y^2 <= 1 evaluated exactly in integers.
