@@ -16,6 +16,8 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+    os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the single JSON line
 
 METRIC = "ssgd_samples_per_s"
 
@@ -171,18 +173,21 @@ def main():
         sampler = ClockSampler(gpu_index=dev.index or 0)
     head = bench_logistic(args, dist, "ssgd", args.steps, args.warmup, backend, X, y, sampler)
     clocks = sampler.summary() if sampler else {}
-    if dist.world == 1 and clocks.get("samples", 0) < 3:
+    few = dist.max_over_ranks(1.0 if (dist.is_main and clocks.get("samples", 0) < 3) else 0.0) > 0
+    if few:
         # the timed region is shorter than nvidia-smi's first sample: replay the SAME step for ~1.5 s (not timed,
-        # not reported) purely to record clocks / throttle reasons under the same load
-        sampler = ClockSampler(gpu_index=dev.index or 0, period_ms=100).start()
-        t_end = time.time() + 1.5
-        while time.time() < t_end:
-            for _ in range(20):
-                head["engine"].step()
-            torch.cuda.synchronize()
-        sampler.stop()
-        clocks = sampler.summary()
-        clocks["window"] = "1.5 s replay of the timed step right after the timed region"
+        # not reported; same step count on every rank) purely to record clocks / throttle reasons under that load
+        replay = max(50, int(1500.0 / max(head["ms_per_step"], 1e-3)))
+        if dist.is_main:
+            sampler = ClockSampler(gpu_index=dev.index or 0, period_ms=100).start()
+        for _ in range(replay):
+            head["engine"].step()
+        torch.cuda.synchronize()
+        dist.barrier()
+        if dist.is_main:
+            sampler.stop()
+            clocks = sampler.summary()
+            clocks["window"] = "%d-step replay of the timed step right after the timed region" % replay
     bytes_per_step = head["samples_per_s"] / dist.world * (head["ms_per_step"] / 1e3) * args.dim * X.element_size()
     out = {
         "metric": METRIC, "value": head["samples_per_s"], "unit": "samples/s", "n_gpus": dist.world,

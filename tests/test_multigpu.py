@@ -1,0 +1,71 @@
+"""In-kernel peer-memory collectives on >= 2 real GPUs (one process per GPU, NCCL only for bootstrap)."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from distributed_algorithm_pyspark_b200.config import ALSConfig, KMeansConfig, LogisticConfig, PageRankConfig
+from distributed_algorithm_pyspark_b200.data.datasets import synthetic_clusters_np
+from distributed_algorithm_pyspark_b200.oracle.algorithms import (LogisticInit, als_draw, als_oracle, kmeans_oracle,
+                                                                   logistic_oracle, pagerank_oracle,
+                                                                   transitive_closure_oracle)
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _torchrun(script, out, nproc, port, *extra):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(HERE, script), str(out), *extra]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert res.returncode == 0, (res.stdout[-2000:], res.stderr[-4000:])
+    return json.loads(open(out).read())
+
+
+def _nproc():
+    import torch
+    return 2 if torch.cuda.device_count() < 4 else 4
+
+
+def test_reference_scripts_fused_multi_gpu(tmp_path, breast_cancer):
+    """The ten algorithms through the fused backend on several GPUs must match the oracle
+    (logical n_slices fixed => independent of the GPU count)."""
+    b = _torchrun("_dist_worker.py", tmp_path / "f.json", 2, 29711, "fused")
+    d = breast_cancer
+    for algo in ["ssgd", "gd", "ma", "bmuf", "easgd"]:
+        cfg = LogisticConfig.for_algo(algo, n_iterations=12, seed=0)
+        ref = logistic_oracle(d.matrix, d.X_test_aug, d.y_test, cfg, LogisticInit.draw(algo, d.dim, cfg.n_slices, 0))
+        np.testing.assert_allclose(b[algo]["w"], ref.w, rtol=1e-7, atol=1e-9)
+        assert b[algo]["bsz"] == ref.batch_sizes
+    assert b["kmeans_toy"] == [[10.0, 2.0], [1.0, 2.0]]
+    pts, _ = synthetic_clusters_np(500, 5, 4, seed=1)
+    km = kmeans_oracle(pts, KMeansConfig(k=4, n_slices=4, n_iterations=4))
+    np.testing.assert_allclose(b["kmeans_syn"]["centers"], km.centers, rtol=1e-9)
+    rs = np.random.RandomState(0)
+    e = list(zip(rs.randint(0, 60, 150).tolist(), rs.randint(0, 60, 150).tolist()))
+    pr = pagerank_oracle(e, PageRankConfig())
+    assert set(map(int, b["pagerank"])) == set(pr)
+    assert max(abs(b["pagerank"][str(k)] - v) / v for k, v in pr.items()) < 1e-4
+    n, rounds, pairs = transitive_closure_oracle(e)
+    assert b["tc"]["n"] == n and b["tc"]["rounds"] == rounds
+    assert sorted(map(tuple, b["tc"]["pairs"])) == sorted(pairs)
+    cfg = ALSConfig(m=40, n=60, k=5, seed=0, n_iterations=3)
+    R, U, V = als_draw(cfg)
+    _, _, errs = als_oracle(R, U, V, cfg)
+    np.testing.assert_allclose(b["als"]["rmse"], errs, rtol=1e-7)
+    from distributed_algorithm_pyspark_b200.models.monte_carlo import accept_count_np
+    assert b["mc"] == accept_count_np(0, 20001, 11)
+
+
+def test_engines_fused_vs_nccl_multi_gpu(tmp_path):
+    out = _torchrun("_engine_worker.py", tmp_path / "e.json", _nproc(), 29712)
+    assert out["allreduce_ok"]
+    for algo, r in out["lr"].items():
+        assert r["rel_diff"] < 5e-3, (algo, r)
+        assert r["bit_identical_across_ranks"], algo
+    assert out["kmeans_rel_diff"] < 1e-3 and out["kmeans_counts_equal"]
+    assert out["pagerank_rel_diff"] < 1e-3
+    assert out["gram_rel_diff"] < 1e-4
