@@ -7,14 +7,29 @@ from .. import _native
 
 
 def supported(X: torch.Tensor, k: int) -> bool:
-    """The tensor-core kernel covers bf16 points with d a multiple of 64 (<= 256) and k a multiple of 256."""
+    """bf16 points with d in {64, 128}, k a multiple of 64 up to 1024, at least one full tile of rows."""
     lib = _native.load()
     if not hasattr(lib, "dapb_kmeans_assign_tc"):
         return False
-    return (X.is_cuda and X.dtype == torch.bfloat16 and X.shape[1] % 64 == 0 and X.shape[1] <= 256
-            and k % 256 == 0 and k <= 4096 and X.shape[0] >= 128)
+    return (X.is_cuda and X.dtype == torch.bfloat16 and X.shape[1] in (64, 128) and k % 64 == 0 and 64 <= k <= 1024
+            and X.shape[0] >= 128 and X.data_ptr() % 16 == 0)
 
 
 class KMeansTC:
-    def __init__(self, X: torch.Tensor, k: int):
-        raise NotImplementedError
+    """Holds the prepared centroid operand; ``assign_accumulate`` = prepare + fused assignment/accumulation."""
+
+    def __init__(self, X: torch.Tensor, k: int, grid: int = 0):
+        self.lib = _native.load()
+        self.X, self.k = X, int(k)
+        self.n, self.d = X.shape
+        self.grid = grid
+        self.b_operand = torch.empty(self.k, self.d, dtype=torch.bfloat16, device=X.device)
+        self.cnorm = torch.empty(self.k, dtype=torch.float32, device=X.device)
+
+    def assign_accumulate(self, centers: torch.Tensor, sums: torch.Tensor, counts: torch.Tensor, assign=None):
+        st = _native.stream_ptr()
+        _native.check(self.lib.dapb_kmeans_tc_prepare(centers.data_ptr(), self.k, self.d, self.b_operand.data_ptr(),
+                                                      self.cnorm.data_ptr(), st), "kmeans_tc_prepare")
+        _native.check(self.lib.dapb_kmeans_assign_tc(self.X.data_ptr(), self.n, self.d, self.b_operand.data_ptr(),
+                                                     self.cnorm.data_ptr(), self.k, _native.ptr(assign), sums.data_ptr(),
+                                                     counts.data_ptr(), self.grid, st), "kmeans_assign_tc")

@@ -1,0 +1,54 @@
+"""Runs one tensor-core kernel check in its own process (a faulting kernel must not poison the pytest process).
+usage: _tc_worker.py kmeans n d k grid | gram n p grid | lr n D grid"""
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from distributed_algorithm_pyspark_b200 import _native  # noqa: E402
+
+
+def kmeans(n, d, k, grid):
+    from distributed_algorithm_pyspark_b200.ops.kmeans_tc import KMeansTC
+    dev = "cuda"
+    torch.manual_seed(n + d + k)
+    centres = torch.randn(k, d, device=dev) * 3
+    lab = torch.randint(0, k, (n,), device=dev)
+    X = (centres[lab] + torch.randn(n, d, device=dev)).to(torch.bfloat16).contiguous()
+    C = (centres + 0.3 * torch.randn(k, d, device=dev)).contiguous()          # current centres (fp32)
+    op = KMeansTC(X, k, grid=grid)
+    sums = torch.zeros(k, d, device=dev)
+    counts = torch.zeros(k, dtype=torch.int32, device=dev)
+    assign = torch.full((n,), -1, dtype=torch.int32, device=dev)
+    op.assign_accumulate(C, sums, counts, assign)
+    torch.cuda.synchronize()
+    cb = C.to(torch.bfloat16).float()
+    cn = (cb * cb).sum(1)
+    dist = cn[None, :] - 2.0 * (X.float() @ cb.T)
+    ref = dist.argmin(1)
+    got = assign.long()
+    bad_range = int(((got < 0) | (got >= k)).sum().item())
+    got_c = got.clamp(0, k - 1)
+    gap = dist.gather(1, got_c[:, None]).squeeze(1) - dist.gather(1, ref[:, None]).squeeze(1)
+    tol = dist.abs().max(1).values * 2.0 ** -11 + 1e-3
+    wrong = int((gap > tol).sum().item())
+    mism = int((got != ref).sum().item())
+    ref_sums = torch.zeros_like(sums).index_add_(0, got_c, X.float())
+    sum_err = float((sums - ref_sums).abs().max().item() / (ref_sums.abs().max().item() + 1e-9))
+    cnt_ok = bool(torch.equal(counts.long(), torch.bincount(got_c, minlength=k)))
+    return {"n": n, "bad_range": bad_range, "wrong": wrong, "mismatch_vs_fp32": mism, "sum_rel_err": sum_err,
+            "counts_ok": cnt_ok, "purity": float((got == lab).float().mean().item())}
+
+
+def main():
+    kind = sys.argv[1]
+    args = list(map(int, sys.argv[2:]))
+    out = {"kmeans": kmeans}[kind](*args)
+    print("RESULT " + json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

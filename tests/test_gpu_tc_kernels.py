@@ -1,0 +1,35 @@
+"""tcgen05 / TMEM / TMA kernels vs plain PyTorch fp32 math.  Each case runs in its own process with a timeout:
+a mis-programmed barrier traps after a bounded wait instead of hanging the box, and a faulted context cannot
+poison the other tests."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def run_case(*args, timeout=180):
+    res = subprocess.run([sys.executable, os.path.join(HERE, "_tc_worker.py"), *map(str, args)], capture_output=True,
+                         text=True, timeout=timeout)
+    assert res.returncode == 0, (res.stdout[-1500:], res.stderr[-3000:])
+    line = [l for l in res.stdout.splitlines() if l.startswith("RESULT ")][-1]
+    return json.loads(line[len("RESULT "):])
+
+
+@pytest.mark.parametrize("n,d,k,grid", [
+    (128, 128, 64, 1),            # one tile, one chunk
+    (512, 128, 128, 1),           # one super tile, two chunks
+    (128 * 4 * 7 + 77, 128, 256, 2),     # several super tiles per CTA (slot / stage / TMEM ring wrap-around) + ragged tail
+    (128 * 37 + 5, 64, 192, 3),          # d = 64, k not a power of two
+    (200000, 128, 1024, 0),              # benchmark-shaped k, full grid
+])
+def test_kmeans_tc_assignment_and_sums(n, d, k, grid):
+    r = run_case("kmeans", n, d, k, grid)
+    assert r["bad_range"] == 0
+    assert r["wrong"] == 0, r                 # every disagreement with fp32 argmin must be a genuine near-tie
+    assert r["mismatch_vs_fp32"] <= max(2, n // 500), r
+    assert r["sum_rel_err"] < 1e-4 and r["counts_ok"], r
