@@ -3,24 +3,25 @@
 //
 // ref math: machine_learning/k-means.py:20-28 (argmin_c ||x - c||, ties -> lowest index) and :57-63
 // (per-cluster vector sum and count).  argmin_c ||x - c||^2 == argmin_c (||c||^2 - 2 x.c); the cross term
-// for a 128-row tile against 64 centroids is one bf16 `tcgen05.mma` chain (M=128, N=64, K=d) whose fp32
+// for a 128-row tile against 128 centroids is one bf16 `tcgen05.mma` chain (M=128, N=128, K=d) whose fp32
 // accumulator lives in TMEM, the centroid operand holds -2c and ||c||^2 is added in the epilogue.
 //
-// Persistent, warp-specialised, one CTA per SM (384 threads):
+// Persistent, warp-specialised, one CTA per SM (512 threads):
 //   warp 0   TMA producer A : 128-row tiles of X (HBM -> smem, 128B swizzle), ring of 5 slots
-//   warp 3   TMA producer B : 64-centroid chunks of the prepared centroid operand (L2 -> smem), ring of 3
+//   warp 3   TMA producer B : 128-centroid chunks of the prepared operand (L2 -> smem), 2 stages
 //   warp 1   MMA issuer     : for each super tile (4 row tiles) x each centroid chunk: 8 x tcgen05.mma
-//   warp 2   TMEM allocator (512 columns = 8 accumulator buffers of 64 columns)
-//   warps 4-7  arg-min epilogue : tcgen05.ld -> (+||c||^2) -> value with the centroid index packed into
-//              the 10 low mantissa bits -> running min per row; the TMEM buffer is released as soon as it
-//              has been copied to registers
-//   warps 8-11 scatter : red.global.add.v4.f32 of every row of the tile (read back from the swizzled
-//              smem tile) into sums[assignment], counts += 1, then the A slot is released
-// A super tile keeps 4 row tiles resident while all centroid chunks stream through, so the centroid
-// operand is re-read from L2 once per 512 rows instead of once per 128.
+//   warp 2   TMEM allocator (512 columns = 4 accumulator buffers of 128 columns), then producer of the ||c||^2 ring
+//   warps 4-7 and 12-15  arg-min epilogue (row tiles 0-1 / 2-3 of the super tile) : tcgen05.ld (32 columns at a time, next load in flight while the current
+//              one is reduced) -> + ||c||^2 (smem ring fed by warp 2) -> value with the column-in-group index in its 5 low mantissa
+//              bits -> running min per row; a TMEM buffer is released as soon as it is in registers
+//   warps 8-11 scatter : red.global.add.v4.f32 of every row (re-read from L2) into sums[assignment], counts += 1
+// A super tile keeps 4 row tiles resident while all centroid chunks stream through, so the centroid operand
+// is re-read from L2 once per 512 rows.  N = 128 per MMA keeps the shared-memory operand traffic
+// ((M + N) * 32 B per 64-cycle MMA = 128 B/clk) within the SM's shared-memory bandwidth; N = 64 was measured
+// at 59 cycles per MMA instead of 32.
 //
-// Near-ties: packing the index costs 10 mantissa bits (relative 2^-13 of the value), which is below the
-// error already introduced by bf16 inputs; exact tie semantics need the CUDA-core path (kmeans.cu).
+// Near-ties: packing the index costs 5 mantissa bits (relative 2^-18 of the value), far below the error already
+// introduced by bf16 inputs; exact tie semantics need the CUDA-core path (kmeans.cu).
 #include "tc_common.cuh"
 
 using namespace dapb;
@@ -29,12 +30,14 @@ using namespace dapb::tc;
 namespace {
 
 constexpr int kTM = 128;          // rows per tile (UMMA M)
-constexpr int kNB = 64;           // centroids per chunk (UMMA N)
+constexpr int kNB = 128;          // centroids per chunk (UMMA N)
 constexpr int kSuper = 4;         // row tiles per super tile
 constexpr int kASlots = 5;
-constexpr int kBStages = 3;
-constexpr int kTBufs = 8;         // TMEM accumulator buffers (8 x 64 columns = 512)
-constexpr int kThreads = 384;
+constexpr int kBStages = 2;
+constexpr int kTBufs = 4;         // TMEM accumulator buffers (4 x 128 columns = 512)
+constexpr int kThreads = 512;        // 16 warps: 4 service warps, 2 x 4 arg-min warps, 4 scatter warps
+constexpr int kParts = kNB / 32;  // 32-column epilogue steps per accumulator
+constexpr int kCnStages = 2;      // ring of centroid-norm chunks in shared memory (indexed constant loads were 3x slower)
 
 template <int KD>
 struct SmemLayout {
@@ -43,55 +46,79 @@ struct SmemLayout {
   static constexpr uint32_t kBChunk = kNB * KD * 2;
   static constexpr uint32_t kAOff = 0;
   static constexpr uint32_t kBOff = kAOff + kASlots * kATile;
-  static constexpr uint32_t kCnOff = kBOff + kBStages * kBChunk;   // float[1024]
-  static constexpr uint32_t kAsOff = kCnOff + 1024 * 4;            // int[kASlots][128]
-  static constexpr uint32_t kBarOff = kAsOff + kASlots * kTM * 4;
-  static constexpr int kNumBars = 2 * kASlots + 2 * kBStages + 2 * kTBufs + kASlots;
+  static constexpr uint32_t kCnOff = kBOff + kBStages * kBChunk;   // float[kCnStages][kNB] ring of ||c||^2 chunks
+  static constexpr uint32_t kAsOff = kCnOff + kCnStages * kNB * 4; // uint16[kASlots][128]
+  static constexpr uint32_t kBarOff = kAsOff + kASlots * kTM * 2;
+  static constexpr int kNumBars = 4 * kASlots + 2 * kBStages + 2 * kTBufs + 2 * kCnStages;
   static constexpr uint32_t kTmemOff = kBarOff + kNumBars * 8;
   static constexpr uint32_t kTotal = kTmemOff + 16;
 };
 
 struct KmTcArgs {
+  const __nv_bfloat16* X; // [n, KD]
   int64_t n;              // rows
-  int k;                  // centroids (multiple of 64, <= 1024)
+  int k;                  // centroids (multiple of 128, <= 1024)
   const float* cnorm;     // [k]
   float* sums;            // [k, KD]
   int* counts;            // [k]
   int* assign;            // [n] or null
+  long long* dbg;         // optional [64] cycle counters written by CTA 0 (profiling aid), or null
+  uint32_t smem_bytes;    // dynamic shared memory actually provided
+  uint32_t keep_mask;     // 0xffffffe0, passed at run time so that (x & mask) | idx stays ONE lop3
 };
+
+// cycle accounting for the profiling aid: adds the cycles spent in stmt to acc when dbg is set
+#define DAPB_T(acc, stmt) do { long long _t0 = prof ? clock64() : 0; stmt; if (prof) acc += clock64() - _t0; } while (0)
+
+__device__ __forceinline__ void bulk_copy_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
 
 template <int KD>
 __global__ void __launch_bounds__(kThreads, 1)
 kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c, KmTcArgs a) {
   using L = SmemLayout<KD>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  // dynamic smem is only guaranteed 16-byte aligned: round up to the 1024 B the 128B swizzle needs
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const uint32_t pad = (1024u - (smem_u32(smem_raw) & 1023u)) & 1023u;   // 128B swizzle needs 1024 B alignment
+  uint8_t* smem = smem_raw + pad;                                          // (keeps the shared address space)
+  if (pad + L::kTotal > a.smem_bytes) {
+    if (threadIdx.x == 0) printf("dapb kmeans_tc: shared memory layout does not fit (pad %u)\n", pad);
+    __trap();
+  }
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
   uint64_t* a_full = bars;
   uint64_t* a_empty = a_full + kASlots;
-  uint64_t* b_full = a_empty + kASlots;
+  uint64_t* as_full = a_empty + kASlots;
+  uint64_t* as_empty = as_full + kASlots;
+  uint64_t* b_full = as_empty + kASlots;
   uint64_t* b_empty = b_full + kBStages;
   uint64_t* t_full = b_empty + kBStages;
   uint64_t* t_empty = t_full + kTBufs;
-  uint64_t* as_full = t_empty + kTBufs;
-  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(smem + L::kTmemOff);
+  uint64_t* cn_full = t_empty + kTBufs;
+  uint64_t* cn_empty = cn_full + kCnStages;
   float* cn_s = reinterpret_cast<float*>(smem + L::kCnOff);
-  int* assign_s = reinterpret_cast<int*>(smem + L::kAsOff);
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(smem + L::kTmemOff);
+  uint16_t* assign_s = reinterpret_cast<uint16_t*>(smem + L::kAsOff);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool prof = a.dbg != nullptr && blockIdx.x == 0;
+  long long pc0 = 0, pc1 = 0, pc2 = 0, pc3 = 0, pc4 = 0;
+  const long long t_start = prof ? clock64() : 0;
   const int64_t n_tiles = (a.n + kTM - 1) / kTM;
   const int64_t n_super = (n_tiles + kSuper - 1) / kSuper;
   const int n_chunks = a.k / kNB;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kASlots; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 5); mbar_init(&as_full[i], 4); }
+    for (int i = 0; i < kASlots; ++i) {
+      mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); mbar_init(&as_full[i], 4); mbar_init(&as_empty[i], 4);
+    }
     for (int i = 0; i < kBStages; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
     for (int i = 0; i < kTBufs; ++i) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], 4); }
+    for (int i = 0; i < kCnStages; ++i) { mbar_init(&cn_full[i], 1); mbar_init(&cn_empty[i], 8); }
     fence_barrier_init();
   }
   if (warp == 2) { tmem_alloc(tmem_holder, 512); tmem_relinquish(); }
-  for (int i = threadIdx.x; i < a.k; i += kThreads) cn_s[i] = a.cnorm[i];
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -107,13 +134,13 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         const int nt = (int)min((int64_t)kSuper, n_tiles - tile0);
         for (int t = 0; t < nt; ++t, ++g) {
           const uint32_t slot = g % kASlots, use = g / kASlots;
-          mbar_wait(&a_empty[slot], (use & 1) ^ 1);
+          DAPB_T(pc0, mbar_wait(&a_empty[slot], (use & 1) ^ 1));
           mbar_arrive_expect_tx(&a_full[slot], L::kATile);
           uint8_t* dst = smem + L::kAOff + slot * L::kATile;
           const int row0 = (int)((tile0 + t) * kTM);
 #pragma unroll
-          for (int h = 0; h < L::kHalves; ++h)
-            tma_load_2d_hint(dst + h * (kTM * 128), &map_x, &a_full[slot], h * 64, row0, kEvictFirst);
+          for (int h = 0; h < L::kHalves; ++h)          // default L2 policy: the scatter warps re-read these rows
+            tma_load_2d(dst + h * (kTM * 128), &map_x, &a_full[slot], h * 64, row0);
         }
       }
     }
@@ -125,7 +152,7 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
         for (int c = 0; c < n_chunks; ++c, ++j) {
           const uint32_t st = j % kBStages, use = j / kBStages;
-          mbar_wait(&b_empty[st], (use & 1) ^ 1);
+          DAPB_T(pc0, mbar_wait(&b_empty[st], (use & 1) ^ 1));
           mbar_arrive_expect_tx(&b_full[st], L::kBChunk);
           uint8_t* dst = smem + L::kBOff + st * L::kBChunk;
 #pragma unroll
@@ -134,95 +161,182 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         }
       }
     }
+  } else if (warp == 2) {
+    // ===================== producer: ||c||^2 chunks for the arg-min warps =====================
+    if (lane == 0) {
+      uint32_t j = 0;
+      for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
+        for (int c = 0; c < n_chunks; ++c, ++j) {
+          const uint32_t st = j % kCnStages, use = j / kCnStages;
+          mbar_wait(&cn_empty[st], (use & 1) ^ 1);
+          mbar_arrive_expect_tx(&cn_full[st], kNB * 4);
+          bulk_copy_g2s(cn_s + st * kNB, a.cnorm + c * kNB, kNB * 4, &cn_full[st]);
+        }
+      }
+    }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc = make_idesc_bf16(kTM, kNB, 0, 0);
+      const uint64_t desc_tmpl = make_smem_desc_sw128(0, 16, 1024);
+      const uint32_t a_base = smem_u32(smem + L::kAOff), b_base = smem_u32(smem + L::kBOff);
+      const bool leader = true;
       uint32_t g0 = 0, j = 0, q = 0;                     // tile / chunk / accumulator counters
-      for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
+      // only lane 0 runs the loop: 32 lanes polling the mbarriers measurably slows the whole SM down (18.1 vs 8.9 ms)
+      const int64_t n_super_mma = lane == 0 ? n_super : 0;
+      for (int64_t s = blockIdx.x; s < n_super_mma; s += gridDim.x) {
         const int64_t tile0 = s * kSuper;
         const int nt = (int)min((int64_t)kSuper, n_tiles - tile0);
         for (int c = 0; c < n_chunks; ++c, ++j) {
           const uint32_t st = j % kBStages;
-          mbar_wait(&b_full[st], (j / kBStages) & 1);
-          const uint32_t b_addr = smem_u32(smem + L::kBOff + st * L::kBChunk);
+          DAPB_T(pc0, mbar_wait(&b_full[st], (j / kBStages) & 1));
           for (int t = 0; t < nt; ++t, ++q) {
             const uint32_t g = g0 + t, slot = g % kASlots;
-            if (c == 0) mbar_wait(&a_full[slot], (g / kASlots) & 1);
+            if (c == 0) DAPB_T(pc1, mbar_wait(&a_full[slot], (g / kASlots) & 1));
             const uint32_t buf = q % kTBufs;
-            mbar_wait(&t_empty[buf], ((q / kTBufs) & 1) ^ 1);
+            DAPB_T(pc2, mbar_wait(&t_empty[buf], ((q / kTBufs) & 1) ^ 1));
             tc_fence_after();
-            const uint32_t a_addr = smem_u32(smem + L::kAOff + slot * L::kATile);
+            // descriptors differ only in the 14-bit start-address field: build the two bases once per step and
+            // add compile-time offsets (units of 16 bytes) for the K halves / K steps
+            const uint64_t da0 = desc_tmpl | (uint64_t)(((a_base + slot * L::kATile) & 0x3FFFF) >> 4);
+            const uint64_t db0 = desc_tmpl | (uint64_t)(((b_base + st * L::kBChunk) & 0x3FFFF) >> 4);
             const uint32_t d_tmem = tmem_base + buf * kNB;
+            if (leader) {
+              DAPB_T(pc3, {
 #pragma unroll
-            for (int h = 0; h < L::kHalves; ++h)
+                for (int h = 0; h < L::kHalves; ++h)
 #pragma unroll
-              for (int ks = 0; ks < 4; ++ks) {
-                const uint64_t da = make_smem_desc_sw128(a_addr + h * (kTM * 128) + ks * 32, 16, 1024);
-                const uint64_t db = make_smem_desc_sw128(b_addr + h * (kNB * 128) + ks * 32, 16, 1024);
-                umma_bf16(d_tmem, da, db, idesc, (h | ks) != 0);
-              }
-            umma_commit(&t_full[buf]);
-            if (c == n_chunks - 1) umma_commit(&a_empty[slot]);     // tensor core is done reading this X tile
+                  for (int ks = 0; ks < 4; ++ks)
+                    umma_bf16(d_tmem, da0 + (uint64_t)((h * (kTM * 128) + ks * 32) >> 4),
+                              db0 + (uint64_t)((h * (kNB * 128) + ks * 32) >> 4), idesc, (h | ks) != 0);
+              });
+              DAPB_T(pc4, {
+                umma_commit(&t_full[buf]);
+                if (c == n_chunks - 1) umma_commit(&a_empty[slot]);   // tensor core is done reading this X tile
+                if (t == nt - 1) umma_commit(&b_empty[st]);           // ... and this centroid chunk
+              });
+            }
           }
-          umma_commit(&b_empty[st]);
         }
         g0 += nt;
       }
     }
-  } else if (warp >= 4 && warp < 8) {
+  } else if ((warp >= 4 && warp < 8) || warp >= 12) {
     // ===================== arg-min epilogue =====================
+    // Two groups of four warps: group 0 (warps 4-7) reduces row tiles 0 and 1 of every super tile, group 1
+    // (warps 12-15) tiles 2 and 3, so every scheduler has two arg-min warps to interleave.  Within a warp the
+    // work is software-pipelined at 32-column granularity: the next TMEM load is in flight while the current 32
+    // values per row are reduced.
     const int qd = warp & 3;                              // TMEM lane quarter this warp may access
+    const int grp = warp >= 12 ? 1 : 0;
+    const int t_lo = grp * 2;                             // first row tile of this group
     const int row = qd * 32 + lane;
-    uint32_t g0 = 0, q = 0;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(qd * 32) << 16);
+    const uint32_t keep = a.keep_mask;
+    uint32_t g0 = 0, q0 = 0, jc = 0;                      // tiles / accumulators / chunks before this super tile
+    uint32_t vA[32], vB[32];
+
+    auto issue_load = [&](uint32_t qq, int part, uint32_t* v) {
+      const uint32_t buf = qq % kTBufs;
+      if (part == 0) {
+        DAPB_T(pc0, mbar_wait(&t_full[buf], (qq / kTBufs) & 1));
+        tc_fence_after();
+      }
+      tmem_ld_32x32b_x32(lane_addr + buf * kNB + part * 32, v);
+    };
+    auto finish_load = [&](uint32_t qq, int part) {       // after the last part the accumulator buffer is free
+      DAPB_T(pc1, tmem_ld_wait());
+      if (part == kParts - 1) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&t_empty[qq % kTBufs]);
+      }
+    };
+    // value | (column within this 32-column group) in the 5 low mantissa bits, ONE lop3 per element
+    // ((x & mask) | imm, LUT 0xEA); which group won is tracked per row
+#define DAPB_PACK(dst, x, J) asm("lop3.b32 %0, %1, %2, " #J ", 0xEA;" : "=r"(dst) : "r"(__float_as_uint(x)), "r"(keep))
+    auto reduce = [&](const uint32_t* v, const float* cn, int group, float m, int& m_group) -> float {
+      const float4* cn4 = reinterpret_cast<const float4*>(cn);
+      float hm = 3.0e38f;
+#ifdef DAPB_KM_EXPERIMENT_NOCN
+#define DAPB_KM_CN(JJ) make_float4(1.f, 2.f, 3.f, 4.f)
+#else
+#define DAPB_KM_CN(JJ) cn4[JJ]
+#endif
+#define DAPB_RED4(JJ, J0, J1, J2, J3) {                                          \
+        const float4 c4 = DAPB_KM_CN(JJ);                                        \
+        uint32_t p0, p1, p2, p3;                                                 \
+        DAPB_PACK(p0, __uint_as_float(v[JJ * 4 + 0]) + c4.x, J0);                \
+        DAPB_PACK(p1, __uint_as_float(v[JJ * 4 + 1]) + c4.y, J1);                \
+        DAPB_PACK(p2, __uint_as_float(v[JJ * 4 + 2]) + c4.z, J2);                \
+        DAPB_PACK(p3, __uint_as_float(v[JJ * 4 + 3]) + c4.w, J3);                \
+        hm = fminf(fminf(hm, __uint_as_float(p0)), fminf(__uint_as_float(p1), fminf(__uint_as_float(p2), __uint_as_float(p3)))); }
+      DAPB_RED4(0, 0, 1, 2, 3) DAPB_RED4(1, 4, 5, 6, 7) DAPB_RED4(2, 8, 9, 10, 11) DAPB_RED4(3, 12, 13, 14, 15)
+      DAPB_RED4(4, 16, 17, 18, 19) DAPB_RED4(5, 20, 21, 22, 23) DAPB_RED4(6, 24, 25, 26, 27) DAPB_RED4(7, 28, 29, 30, 31)
+#undef DAPB_RED4
+      if (hm < m) { m = hm; m_group = group; }            // strict '<': the earlier (lower-index) group wins ties
+      return m;
+    };
+
     for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
       const int64_t tile0 = s * kSuper;
       const int nt = (int)min((int64_t)kSuper, n_tiles - tile0);
-      float best[kSuper];
+      float best[2] = {3.0e38f, 3.0e38f};
+      int bgrp[2] = {0, 0};
+      // accumulator index of (chunk c, row tile t) in this super tile: q0 + c * nt + t
+      if (nt == kSuper) {
+        issue_load(q0 + t_lo, 0, vA);
+        for (int c = 0; c < n_chunks; ++c, ++jc) {
+          const uint32_t cst = jc % kCnStages;
+          mbar_wait(&cn_full[cst], (jc / kCnStages) & 1);
+          const float* cn = cn_s + cst * kNB;
 #pragma unroll
-      for (int t = 0; t < kSuper; ++t) best[t] = 3.0e38f;
-      for (int c = 0; c < n_chunks; ++c) {
-#pragma unroll
-        for (int t = 0; t < kSuper; ++t) {
-          if (t < nt) {
-            const uint32_t buf = q % kTBufs;
-            mbar_wait(&t_full[buf], (q / kTBufs) & 1);
-            tc_fence_after();
-            uint32_t v[kNB];
-            const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + buf * kNB;
-            tmem_ld_32x32b_x32(taddr, v);
-            tmem_ld_32x32b_x32(taddr + 32, v + 32);
-            tmem_ld_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&t_empty[buf]);      // accumulator copied out: MMA may overwrite it
-            float m = best[t];
-            const float4* cn4 = reinterpret_cast<const float4*>(cn_s + c * kNB);
-#pragma unroll
-            for (int jj = 0; jj < kNB / 4; ++jj) {
-              const float4 cn = cn4[jj];
-              const uint32_t idx = (uint32_t)(c * kNB + jj * 4);
-              float x0 = __uint_as_float(v[jj * 4 + 0]) + cn.x;
-              float x1 = __uint_as_float(v[jj * 4 + 1]) + cn.y;
-              float x2 = __uint_as_float(v[jj * 4 + 2]) + cn.z;
-              float x3 = __uint_as_float(v[jj * 4 + 3]) + cn.w;
-              x0 = __uint_as_float((__float_as_uint(x0) & 0xfffffc00u) | (idx + 0));
-              x1 = __uint_as_float((__float_as_uint(x1) & 0xfffffc00u) | (idx + 1));
-              x2 = __uint_as_float((__float_as_uint(x2) & 0xfffffc00u) | (idx + 2));
-              x3 = __uint_as_float((__float_as_uint(x3) & 0xfffffc00u) | (idx + 3));
-              m = fminf(fminf(m, x0), fminf(x1, fminf(x2, x3)));
-            }
-            best[t] = m;
-            ++q;
+          for (int tt = 0; tt < 2; ++tt) {
+            const uint32_t qq = q0 + c * kSuper + t_lo + tt;
+            // the accumulator that follows (c, t_lo + 1) for this group is (c + 1, t_lo)
+            const uint32_t qn = tt == 0 ? qq + 1 : qq + kSuper - 1;
+            const bool has_next = tt == 0 || c + 1 < n_chunks;
+            finish_load(qq, 0); issue_load(qq, 1, vB);
+            best[tt] = reduce(vA, cn, c * kParts + 0, best[tt], bgrp[tt]);
+            finish_load(qq, 1); issue_load(qq, 2, vA);
+            best[tt] = reduce(vB, cn + 32, c * kParts + 1, best[tt], bgrp[tt]);
+            finish_load(qq, 2); issue_load(qq, 3, vB);
+            best[tt] = reduce(vA, cn + 64, c * kParts + 2, best[tt], bgrp[tt]);
+            finish_load(qq, 3);
+            if (has_next) issue_load(qn, 0, vA);
+            best[tt] = reduce(vB, cn + 96, c * kParts + 3, best[tt], bgrp[tt]);
           }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&cn_empty[cst]);     // this warp is done with the chunk's norms
+        }
+      } else {                                            // ragged last super tile: simple path
+        for (int c = 0; c < n_chunks; ++c, ++jc) {
+          const uint32_t cst = jc % kCnStages;
+          mbar_wait(&cn_full[cst], (jc / kCnStages) & 1);
+          const float* cn = cn_s + cst * kNB;
+#pragma unroll
+          for (int tt = 0; tt < 2; ++tt) {
+            if (t_lo + tt < nt) {
+              const uint32_t qq = q0 + c * nt + t_lo + tt;
+#pragma unroll
+              for (int part = 0; part < kParts; ++part) {
+                issue_load(qq, part, vA); finish_load(qq, part);
+                best[tt] = reduce(vA, cn + part * 32, c * kParts + part, best[tt], bgrp[tt]);
+              }
+            }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&cn_empty[cst]);
         }
       }
 #pragma unroll
-      for (int t = 0; t < kSuper; ++t) {
+      for (int tt = 0; tt < 2; ++tt) {
+        const int t = t_lo + tt;
         if (t < nt) {
           const uint32_t g = g0 + t, slot = g % kASlots;
-          const int cidx = (int)(__float_as_uint(best[t]) & 1023u);
-          assign_s[slot * kTM + row] = cidx;
+          const int cidx = bgrp[tt] * 32 + (int)(__float_as_uint(best[tt]) & 31u);
+          mbar_wait(&as_empty[slot], ((g / kASlots) & 1) ^ 1);     // scatter warps are done with the previous use
+          assign_s[slot * kTM + row] = (uint16_t)cidx;
           const int64_t grow = (tile0 + t) * kTM + row;
           if (a.assign && grow < a.n) a.assign[grow] = cidx;
           __syncwarp();
@@ -230,8 +344,10 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         }
       }
       g0 += nt;
+      q0 += (uint32_t)(n_chunks * nt);
     }
-  } else if (warp >= 8) {
+#undef DAPB_PACK
+  } else if (warp >= 8 && warp < 12) {
     // ===================== scatter: sums[assign[row]] += x[row], counts += 1 =====================
     const int qd = warp & 3;
     uint32_t g = 0;
@@ -240,35 +356,52 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       const int nt = (int)min((int64_t)kSuper, n_tiles - tile0);
       for (int t = 0; t < nt; ++t, ++g) {
         const uint32_t slot = g % kASlots, par = (g / kASlots) & 1;
-        mbar_wait(&a_full[slot], par);                      // acquire the TMA-written tile
-        mbar_wait(&as_full[slot], par);
-        const uint8_t* tile = smem + L::kAOff + slot * L::kATile;
-        const int64_t row_base = (tile0 + t) * kTM;
-        for (int i = 0; i < 32; ++i) {
-          const int r = qd * 32 + i;
-          if (row_base + r >= a.n) break;
-          const int cidx = assign_s[slot * kTM + r];
+        DAPB_T(pc0, mbar_wait(&as_full[slot], par));
+        const int64_t row_base = (tile0 + t) * kTM + qd * 32;
+        const int my_c = (int)assign_s[slot * kTM + qd * 32 + lane];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&as_empty[slot]);        // assignments are in registers
+        if (row_base + lane < a.n) atomicAdd(a.counts + my_c, 1);
+        const int n_rows = (int)max((int64_t)0, min((int64_t)32, a.n - row_base));
+        constexpr int kP = (KD + 127) / 128;                // 128-feature passes per row (1 for d <= 128)
+        const bool lane_on = lane * 4 < KD || kP > 1;
+        // batches of 8 rows: all loads of a batch are issued before the first atomic, so one L2 round trip is
+        // paid per batch instead of per row
+        for (int i0 = 0; i0 < n_rows; i0 += 8) {
+          uint2 raw[8][kP];
 #pragma unroll
-          for (int p = 0; p < KD / 128 + (KD < 128 ? 1 : 0); ++p) {
-            const int col = p * 128 + lane * 4;             // 4 consecutive features per lane
-            if (col < KD) {
-              const int h = col >> 6, cb = (col & 63) * 2;  // 64-column half, byte offset inside the 128 B row
-              const int chunk = cb >> 4, within = cb & 15;
-              const uint2 raw = *reinterpret_cast<const uint2*>(tile + h * (kTM * 128) + r * 128 +
-                                                                 ((chunk ^ (r & 7)) << 4) + within);
-              float* dst = a.sums + (size_t)cidx * KD + col;
-              asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "f"(bf16_lo(raw.x)),
-                           "f"(bf16_hi(raw.x)), "f"(bf16_lo(raw.y)), "f"(bf16_hi(raw.y)) : "memory");
+          for (int u = 0; u < 8; ++u) {
+            const __nv_bfloat16* xr = a.X + (row_base + min(i0 + u, n_rows - 1)) * (int64_t)KD;
+#pragma unroll
+            for (int p = 0; p < kP; ++p) {
+              const int col = p * 128 + lane * 4;           // 4 consecutive features per lane
+              raw[u][p] = (col < KD) ? __ldg(reinterpret_cast<const uint2*>(xr + col)) : make_uint2(0u, 0u);
             }
           }
-          if (lane == 0) atomicAdd(a.counts + cidx, 1);
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int cidx = __shfl_sync(0xffffffffu, my_c, min(i0 + u, 31));
+            if (i0 + u < n_rows && lane_on) {
+#pragma unroll
+              for (int p = 0; p < kP; ++p) {
+                const int col = p * 128 + lane * 4;
+                if (col < KD) {
+                  float* dst = a.sums + (size_t)cidx * KD + col;
+                  asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "f"(bf16_lo(raw[u][p].x)),
+                               "f"(bf16_hi(raw[u][p].x)), "f"(bf16_lo(raw[u][p].y)), "f"(bf16_hi(raw[u][p].y)) : "memory");
+                }
+              }
+            }
+          }
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&a_empty[slot]);
       }
     }
   }
 
+  if (prof && lane == 0 && (warp <= 4 || warp == 8)) {   // one representative warp per role
+    long long* d = a.dbg + (warp == 8 ? 5 : warp) * 8;
+    d[0] = pc0; d[1] = pc1; d[2] = pc2; d[3] = pc3; d[5] = pc4; d[4] = clock64() - t_start;
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == 2) tmem_dealloc(tmem_base, 512);
@@ -293,9 +426,10 @@ __global__ void kmeans_tc_prep_kernel(const float* __restrict__ C, int k, int d,
 }
 
 template <int KD>
-int launch_km(const CUtensorMap& mx, const CUtensorMap& mc, const KmTcArgs& a, int grid, cudaStream_t st) {
-  constexpr uint32_t smem = SmemLayout<KD>::kTotal + 1024;
-  static_assert(smem <= 227 * 1024, "k-means tensor-core kernel exceeds shared memory");
+int launch_km(const CUtensorMap& mx, const CUtensorMap& mc, KmTcArgs a, int grid, cudaStream_t st) {
+  constexpr uint32_t smem = (SmemLayout<KD>::kTotal + 1024 <= 227 * 1024) ? SmemLayout<KD>::kTotal + 1024 : 227 * 1024;
+  static_assert(SmemLayout<KD>::kTotal <= 227 * 1024, "k-means tensor-core kernel exceeds shared memory");
+  a.smem_bytes = smem;
   DAPB_CUDA_CHECK(cudaFuncSetAttribute(kmeans_tc_kernel<KD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kmeans_tc_kernel<KD><<<grid, kThreads, smem, st>>>(mx, mc, a);
   DAPB_LAUNCH_CHECK();
@@ -318,16 +452,25 @@ extern "C" int dapb_kmeans_tc_prepare(const float* centers, int32_t k, int32_t d
 extern "C" int dapb_kmeans_assign_tc(const void* X, int64_t n, int32_t d, const void* b_operand, const float* cnorm,
                                      int32_t k, int32_t* assign, float* sums, int32_t* counts, int32_t grid,
                                      void* stream) {
+  return dapb_kmeans_assign_tc_dbg(X, n, d, b_operand, cnorm, k, assign, sums, counts, grid, nullptr, stream);
+}
+
+// Same, with an optional device buffer of 64 int64 cycle counters filled by CTA 0 (per-role wait times):
+// [role*8 + i], roles 0 X-producer, 1 MMA issuer, 3 centroid-producer, 4 arg-min warp, 5 scatter warp;
+// i = 0..2 wait counters, 3 MMA issue, 5 commits, 4 = total cycles.  Used by scripts/kmeans_tc_probe.py.
+extern "C" int dapb_kmeans_assign_tc_dbg(const void* X, int64_t n, int32_t d, const void* b_operand,
+                                         const float* cnorm, int32_t k, int32_t* assign, float* sums,
+                                         int32_t* counts, int32_t grid, long long* dbg, void* stream) {
   DAPB_REQUIRE(X && b_operand && cnorm && sums && counts, "kmeans_assign_tc: null argument");
   DAPB_REQUIRE(d == 64 || d == 128, "kmeans_assign_tc: d must be 64 or 128 (got %d)", d);
-  DAPB_REQUIRE(k >= 64 && k <= 1024 && k % 64 == 0, "kmeans_assign_tc: k must be a multiple of 64 in [64, 1024] (got %d)", k);
+  DAPB_REQUIRE(k >= 128 && k <= 1024 && k % 128 == 0, "kmeans_assign_tc: k must be a multiple of 128 in [128, 1024] (got %d)", k);
   DAPB_REQUIRE(n >= 1 && n < (1ll << 31) - 256, "kmeans_assign_tc: n out of range for 32-bit TMA coordinates");
   CUtensorMap mx, mc;
   int rc = make_tensor_map_bf16_2d(&mx, X, (uint64_t)n, (uint64_t)d, (uint64_t)d, 64, kTM);
   if (rc) return rc;
   rc = make_tensor_map_bf16_2d(&mc, b_operand, (uint64_t)k, (uint64_t)d, (uint64_t)d, 64, kNB);
   if (rc) return rc;
-  KmTcArgs a{n, k, cnorm, sums, counts, assign};
+  KmTcArgs a{(const __nv_bfloat16*)X, n, k, cnorm, sums, counts, assign, dbg, 0, 0xffffffe0u};
   if (grid <= 0) grid = dapb::sm_count();
   const int64_t n_super = ((n + kTM - 1) / kTM + kSuper - 1) / kSuper;
   if (grid > n_super) grid = (int)n_super;

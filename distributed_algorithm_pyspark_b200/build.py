@@ -51,7 +51,8 @@ def _compile(src: Path, verbose: bool, ptxas_v: bool) -> Path:
     newest = max(src.stat().st_mtime, _headers_mtime())
     if obj.exists() and obj.stat().st_mtime >= newest:
         return obj
-    cmd = [nvcc_path(), *ARCH_FLAGS, *COMMON_FLAGS, *PER_FILE.get(src.name, []), "-c", str(src), "-o", str(obj)]
+    extra = os.environ.get("DAPB_EXTRA_NVCC_FLAGS", "").split()      # experiments only
+    cmd = [nvcc_path(), *ARCH_FLAGS, *COMMON_FLAGS, *PER_FILE.get(src.name, []), *extra, "-c", str(src), "-o", str(obj)]
     if ptxas_v:
         cmd += ["-Xptxas", "-v"]
     if verbose:

@@ -7,11 +7,11 @@ from .. import _native
 
 
 def supported(X: torch.Tensor, k: int) -> bool:
-    """bf16 points with d in {64, 128}, k a multiple of 64 up to 1024, at least one full tile of rows."""
+    """bf16 points with d in {64, 128}, k a multiple of 128 up to 1024, at least one full tile of rows."""
     lib = _native.load()
     if not hasattr(lib, "dapb_kmeans_assign_tc"):
         return False
-    return (X.is_cuda and X.dtype == torch.bfloat16 and X.shape[1] in (64, 128) and k % 64 == 0 and 64 <= k <= 1024
+    return (X.is_cuda and X.dtype == torch.bfloat16 and X.shape[1] in (64, 128) and k % 128 == 0 and 128 <= k <= 1024
             and X.shape[0] >= 128 and X.data_ptr() % 16 == 0)
 
 

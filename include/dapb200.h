@@ -171,13 +171,16 @@ DAPB_API int dapb_kmeans_finalize(const DapbComm* comm, void* sums, int32_t* cou
                                   int32_t d, int32_t f64, uint64_t payload_off, uint32_t flag_base,
                                   uint64_t epoch, int32_t* counts_out, int32_t clear_partials, void* stream);
 DAPB_API uint64_t dapb_kmeans_payload_bytes(int32_t world, int32_t k, int32_t d, int32_t elem_bytes);
-/* Tensor-core assignment (tcgen05.mma + TMEM + TMA), bf16 points, d in {64,128}, k multiple of 64 <= 1024.
+/* Tensor-core assignment (tcgen05.mma + TMEM + TMA), bf16 points, d in {64,128}, k multiple of 128 <= 1024.
  * dapb_kmeans_tc_prepare turns fp32 centres into the bf16 operand (-2c) [k,d] and ||bf16(c)||^2 [k]. */
 DAPB_API int dapb_kmeans_tc_prepare(const float* centers, int32_t k, int32_t d, void* b_operand, float* cnorm,
                                     void* stream);
 DAPB_API int dapb_kmeans_assign_tc(const void* X, int64_t n, int32_t d, const void* b_operand, const float* cnorm,
                                    int32_t k, int32_t* assign, float* sums, int32_t* counts, int32_t grid,
                                    void* stream);
+DAPB_API int dapb_kmeans_assign_tc_dbg(const void* X, int64_t n, int32_t d, const void* b_operand,
+                                       const float* cnorm, int32_t k, int32_t* assign, float* sums,
+                                       int32_t* counts, int32_t grid, long long* dbg, void* stream);
 
 /* ------------------------------------------------------------------ F4 PageRank -----------
  * ref: graph_computation/pagerank.py:21-25,44-57.  Contribution vector [2][V] float lives in the

@@ -21,10 +21,10 @@ def run_case(*args, timeout=180):
 
 
 @pytest.mark.parametrize("n,d,k,grid", [
-    (128, 128, 64, 1),            # one tile, one chunk
-    (512, 128, 128, 1),           # one super tile, two chunks
+    (128, 128, 128, 1),           # one tile, one chunk
+    (512, 128, 256, 1),           # one super tile, two chunks
     (128 * 4 * 7 + 77, 128, 256, 2),     # several super tiles per CTA (slot / stage / TMEM ring wrap-around) + ragged tail
-    (128 * 37 + 5, 64, 192, 3),          # d = 64, k not a power of two
+    (128 * 37 + 5, 64, 384, 3),          # d = 64, k not a power of two
     (200000, 128, 1024, 0),              # benchmark-shaped k, full grid
 ])
 def test_kmeans_tc_assignment_and_sums(n, d, k, grid):
