@@ -102,6 +102,8 @@ def _declare(lib: C.CDLL):
         "dapb_tc_exchange": (C.c_int, [P(DapbComm), vp, u64, u64, u32, u64, vp]),
         "dapb_tc_drain": (C.c_int, [P(DapbComm), vp, u64, vp, vp, u64, u64, vp]),
         "dapb_gram": (C.c_int, [P(DapbComm), vp, vp, i64, i32, i32, i64, i64, i32, vp, i32, vp, vp, u64, u32, u64, i32, vp]),
+        "dapb_gram_tc": (C.c_int, [P(DapbComm), vp, i64, i32, vp, vp, i32, u64, u32, u64, i32, vp]),
+        "dapb_gram_tc_payload_bytes": (u64, [i32, i32]),
         "dapb_rows_times_small": (C.c_int, [vp, vp, i64, i32, i32, i64, i32, i32, vp, vp]),
         "dapb_solve_rows": (C.c_int, [vp, f64, vp, i64, i32, i32, vp, vp]),
         "dapb_sq_residual": (C.c_int, [vp, vp, vp, i64, i32, i32, i32, vp, vp]),

@@ -10,9 +10,33 @@ def supported(A: torch.Tensor) -> bool:
     lib = _native.load()
     if not hasattr(lib, "dapb_gram_tc"):
         return False
-    return A.is_cuda and A.dtype == torch.bfloat16 and A.shape[1] == 512 and A.shape[0] >= 4096
+    return (A.is_cuda and A.dtype == torch.bfloat16 and A.dim() == 2 and A.is_contiguous() and A.shape[1] in (128, 256, 512)
+            and A.shape[0] >= 64 and A.data_ptr() % 16 == 0)
 
 
 class GramTC:
-    def __init__(self, A: torch.Tensor, dist):
-        raise NotImplementedError
+    """``G = A^T A`` summed over every rank's rows, result replicated (fp32 [P, P])."""
+
+    def __init__(self, A: torch.Tensor, dist=None, heap=None, splits: int = 0):
+        from ..parallel.dist import current
+        self.dist = dist or current()
+        self.lib = _native.load()
+        self.A = A
+        self.n, self.P = A.shape
+        self.splits = splits
+        self.G = torch.zeros(self.P, self.P, dtype=torch.float32, device=A.device)
+        self.tickets = torch.zeros(self.P // 128, dtype=torch.int32, device=A.device)
+        self.region = None
+        from ..parallel.symm import default_heap
+        self.heap = heap or default_heap()
+        if self.dist.world > 1:
+            nbytes = int(self.lib.dapb_gram_tc_payload_bytes(self.dist.world, self.P))
+            self.region = self.heap.region(f"gram_tc_{self.P}", nbytes, (self.P // 128) * _native.MAX_RANKS)
+
+    def __call__(self, allreduce: bool = True) -> torch.Tensor:
+        reg = self.region
+        _native.check(self.lib.dapb_gram_tc(self.heap.comm_ref(), self.A.data_ptr(), self.n, self.P, self.G.data_ptr(),
+                                            self.tickets.data_ptr(), self.splits, reg.payload_off if reg else 0,
+                                            reg.flag_base if reg else 0, reg.next_epoch() if (reg and allreduce) else 1,
+                                            int(allreduce), _native.stream_ptr()), "gram_tc")
+        return self.G

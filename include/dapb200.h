@@ -217,6 +217,12 @@ DAPB_API int dapb_gram(const DapbComm* comm, const void* X, const void* Y, int64
                        int64_t ldx, int64_t ldy, int32_t dtype, void* partial, int32_t splits, void* C,
                        uint32_t* ticket, uint64_t payload_off, uint32_t flag_base, uint64_t epoch,
                        int32_t do_allreduce, void* stream);
+/* Tensor-core Gram (tcgen05.mma, MN-major operands straight from one TMA tile): G = A^T A, A [n_rows, P] bf16,
+ * P in {128, 256, 512}; row splits are reduced with vector atomics, ranks with an in-kernel one-shot all-reduce. */
+DAPB_API int dapb_gram_tc(const DapbComm* comm, const void* A, int64_t n_rows, int32_t P, float* G, uint32_t* tickets,
+                          int32_t splits, uint64_t payload_off, uint32_t flag_base, uint64_t epoch,
+                          int32_t do_allreduce, void* stream);
+DAPB_API uint64_t dapb_gram_tc_payload_bytes(int32_t world, int32_t P);
 DAPB_API int dapb_rows_times_small(const void* R, const void* V, int64_t m, int32_t n, int32_t k, int64_t ldr,
                                    int32_t transpose_r, int32_t f64, void* out, void* stream);
 DAPB_API int dapb_solve_rows(const void* G, double ridge, const void* B, int64_t m, int32_t k, int32_t f64,

@@ -43,10 +43,28 @@ def kmeans(n, d, k, grid):
             "counts_ok": cnt_ok, "purity": float((got == lab).float().mean().item())}
 
 
+def gram(n, P, splits):
+    from distributed_algorithm_pyspark_b200.ops.gram_tc import GramTC
+    from distributed_algorithm_pyspark_b200.parallel.dist import init_distributed
+    dist = init_distributed()
+    dev = "cuda"
+    torch.manual_seed(n + P)
+    A = torch.randn(n, P, device=dev).to(torch.bfloat16).contiguous()
+    op = GramTC(A, dist, splits=splits)
+    G1 = op().clone()
+    G2 = op().clone()                       # second call: tickets / accumulator state must have been reset
+    torch.cuda.synchronize()
+    ref = A.double().T @ A.double()
+    scale = float(ref.abs().max().item())
+    return {"err1": float((G1.double() - ref).abs().max().item()) / scale,
+            "err2": float((G2.double() - ref).abs().max().item()) / scale,
+            "sym": float((G1 - G1.T).abs().max().item()) / scale}
+
+
 def main():
     kind = sys.argv[1]
     args = list(map(int, sys.argv[2:]))
-    out = {"kmeans": kmeans}[kind](*args)
+    out = {"kmeans": kmeans, "gram": gram}[kind](*args)
     print("RESULT " + json.dumps(out))
 
 

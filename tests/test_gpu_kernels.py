@@ -295,6 +295,15 @@ def test_solve_rows_and_cholesky_vs_torch(lib):
         ref = torch.linalg.solve(G + 0.5 * torch.eye(k, device=DEV, dtype=dt), B.T).T
         np.testing.assert_allclose(Xo.cpu().numpy(), ref.cpu().numpy(), rtol=1e-3 if dt == torch.float32 else 1e-9,
                                    atol=1e-4 if dt == torch.float32 else 1e-11)
+    for n, dt, tol in [(96, torch.float64, 1e-9), (75, torch.float64, 1e-9), (512, torch.float32, 2e-3)]:
+        A = torch.randn(4 * n, n, device=DEV, dtype=dt)
+        G = (A.T @ A).contiguous()
+        L = G.clone()
+        info = torch.zeros(1, dtype=torch.int32, device=DEV)
+        _native.check(lib.dapb_cholesky(L.data_ptr(), n, int(dt == torch.float64), info.data_ptr(), _native.stream_ptr()))
+        assert int(info.item()) == 0
+        ref = torch.linalg.cholesky(G)
+        np.testing.assert_allclose(L.cpu().numpy(), ref.cpu().numpy(), rtol=tol, atol=tol * float(ref.abs().max()))
     n = 96
     A = torch.randn(400, n, device=DEV, dtype=torch.float64)
     G = (A.T @ A).contiguous()

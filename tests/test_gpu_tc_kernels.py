@@ -33,3 +33,16 @@ def test_kmeans_tc_assignment_and_sums(n, d, k, grid):
     assert r["wrong"] == 0, r                 # every disagreement with fp32 argmin must be a genuine near-tie
     assert r["mismatch_vs_fp32"] <= max(2, n // 500), r
     assert r["sum_rel_err"] < 1e-4 and r["counts_ok"], r
+
+
+@pytest.mark.parametrize("n,P,splits", [
+    (64, 128, 1),              # one stage, one strip
+    (64 * 7 + 13, 256, 2),     # ring wrap-around + ragged last tile, two strips
+    (5000, 512, 3),            # full-width strip (all 512 TMEM columns), uneven splits
+    (300000, 512, 0),          # benchmark-shaped width, full grid
+])
+def test_gram_tc_vs_fp64(n, P, splits):
+    r = run_case("gram", n, P, splits)
+    tol = 2e-5 if n < 100000 else 1e-4        # fp32 accumulation over n rows
+    assert r["err1"] < tol and r["err2"] < tol, r
+    assert r["sym"] < tol, r
