@@ -16,8 +16,8 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-    os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the single JSON line
+if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
+    os.environ.pop("NCCL_DEBUG", None)         # VERSION / WARN print a banner on stdout; keep it to the JSON line
 
 METRIC = "ssgd_samples_per_s"
 

@@ -85,7 +85,7 @@ class ShardedPageRank:
         if backend == "fused":
             from ..parallel.symm import default_heap
             self.lib = _native.load()
-            self.heap = heap or default_heap(max(64 << 20, 2 * graph.V * 4 + (8 << 20)))
+            self.heap = heap or default_heap(max(1 << 30, 2 * graph.V * 4 + (64 << 20)))
             self.region = self.heap.region(f"pagerank_V{graph.V}", 2 * graph.V * 4, _native.MAX_RANKS)
             self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)
         else:

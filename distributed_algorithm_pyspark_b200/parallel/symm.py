@@ -132,11 +132,14 @@ class _CudaArray:
 _DEFAULT: Optional[SymmetricHeap] = None
 
 
-def default_heap(nbytes: int = 64 << 20) -> SymmetricHeap:
-    """Process-wide heap, created on first use (collective across ranks!)."""
+def default_heap(nbytes: int = 1 << 30) -> SymmetricHeap:
+    """Process-wide heap (1 GiB of the 180 GB by default), created on first use (collective across ranks!).
+    ``DAPB_HEAP_MB`` overrides the size."""
     global _DEFAULT
     if _DEFAULT is None:
-        _DEFAULT = SymmetricHeap(nbytes)
+        import os
+        mb = os.environ.get("DAPB_HEAP_MB")
+        _DEFAULT = SymmetricHeap(int(mb) << 20 if mb else nbytes)
     return _DEFAULT
 
 
