@@ -9,6 +9,9 @@
 // sinks receive rank but their mass is dropped.  Vector form:
 //      s[v] = sum_{u->v} c[u];  r[v] = s[v] > 0 ? q/n + (1-q) s[v] : 0;  c'[v] = r[v] / outdeg[v].
 //
+// Work split: rows are grouped on the host into blocks of ~2048 non-zeros (models/pagerank.py), so the skewed
+// R-MAT degree distribution is balanced by construction.
+//
 // Sharding: rank g owns destination vertices [v0, v1) and the CSR rows of A^T for them; the
 // contribution vector c (all V entries) is replicated in the symmetric heap, double-buffered on the
 // iteration parity: iteration t reads buffer t&1 and pushes into buffer (t+1)&1 of every rank.
@@ -19,14 +22,14 @@ using namespace dapb;
 namespace {
 
 constexpr int kPrThreads = 256;
-constexpr int kGroup = 8;            // lanes per light row
+constexpr int kPrCap = 4096;         // gathered contributions staged per row block (16 KB of shared memory)
 
 struct PrArgs {
   const int64_t* row_ptr;   // [nv_local + 1], offsets into col_idx
   const int32_t* col_idx;   // [nnz_local] source vertex ids (global)
   const float* inv_outdeg;  // [nv_local] 1/outdeg of the OWNED vertices (0 for sinks)
-  const int32_t* heavy;     // [n_heavy] local row ids with degree >= heavy threshold (may be null)
-  int32_t n_heavy, heavy_threshold;
+  const int32_t* blocks;    // [n_blocks + 1] row boundaries: block b covers rows [blocks[b], blocks[b+1])
+  int32_t n_blocks;
   int64_t nv_local, v0, V;
   float base, damp;         // q/n and (1-q)
   float* ranks_local;       // [nv_local] out
@@ -52,7 +55,13 @@ __device__ __forceinline__ void pr_finish_row(const PrArgs& a, const DapbComm& c
   }
 }
 
+// CSR-stream SpMV: a CTA takes a block of consecutive rows holding <= kPrCap non-zeros, gathers ALL their
+// contributions with perfectly parallel, coalesced index reads (many independent loads in flight per thread),
+// stages them in shared memory, and then one thread per row sums its segment and runs the fused epilogue
+// (consecutive threads -> consecutive vertices -> coalesced local and peer stores).  Blocks that contain a
+// row longer than the staging buffer fall back to a CTA-wide strided sum per row.
 __global__ void __launch_bounds__(kPrThreads) pagerank_step_kernel(PrArgs a, DapbComm c) {
+  __shared__ float vals[kPrCap];
   __shared__ float s_red[kPrThreads / 32];
   __shared__ bool s_last;
   const int tid = threadIdx.x;
@@ -65,40 +74,52 @@ __global__ void __launch_bounds__(kPrThreads) pagerank_step_kernel(PrArgs a, Dap
     __syncthreads();
   }
 
-  // ---- heavy rows first: one CTA per row, whole block strides over the row ----------------------
-  for (int h = blockIdx.x; h < a.n_heavy; h += gridDim.x) {
-    const int64_t row = a.heavy[h];
-    const int64_t e0 = a.row_ptr[row], e1 = a.row_ptr[row + 1];
-    float s = 0.f;
-    for (int64_t e = e0 + tid; e < e1; e += kPrThreads) s += __ldcg(c_cur + a.col_idx[e]);
-    s = warp_sum(s);
-    if ((tid & 31) == 0) s_red[tid >> 5] = s;
-    __syncthreads();
-    if (tid == 0) {
-      float t = 0.f;
+  for (int blk = blockIdx.x; blk < a.n_blocks; blk += gridDim.x) {
+    const int r0 = a.blocks[blk], r1 = a.blocks[blk + 1];
+    if (r0 >= r1) continue;
+    const int64_t e0 = a.row_ptr[r0], e1 = a.row_ptr[r1];
+    const int nnz = (int)min(e1 - e0, (int64_t)(kPrCap + 1));
+    if (nnz <= kPrCap) {
+      const int32_t* ci = a.col_idx + e0;
+      int i = tid;
+      for (; i + 3 * kPrThreads < nnz; i += 4 * kPrThreads) {          // 4 independent gathers in flight
+        const int32_t u0 = ci[i], u1 = ci[i + kPrThreads], u2 = ci[i + 2 * kPrThreads], u3 = ci[i + 3 * kPrThreads];
+        const float f0 = __ldcg(c_cur + u0), f1 = __ldcg(c_cur + u1), f2 = __ldcg(c_cur + u2), f3 = __ldcg(c_cur + u3);
+        vals[i] = f0; vals[i + kPrThreads] = f1; vals[i + 2 * kPrThreads] = f2; vals[i + 3 * kPrThreads] = f3;
+      }
+      for (; i < nnz; i += kPrThreads) vals[i] = __ldcg(c_cur + ci[i]);
+      __syncthreads();
+      for (int r = r0 + tid; r < r1; r += kPrThreads) {
+        const int b0 = (int)(a.row_ptr[r] - e0), b1 = (int)(a.row_ptr[r + 1] - e0);
+        float s = 0.f;
+        for (int j = b0; j < b1; ++j) s += vals[j];
+        pr_finish_row(a, c, c_next_local, r, s);
+      }
+      __syncthreads();
+    } else {
+      for (int r = r0; r < r1; ++r) {                                   // block with a very long row
+        const int64_t b0 = a.row_ptr[r], b1 = a.row_ptr[r + 1];
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        int64_t e = b0 + tid;
+        for (; e + 3 * kPrThreads < b1; e += 4 * kPrThreads) {
+          s0 += __ldcg(c_cur + a.col_idx[e]);
+          s1 += __ldcg(c_cur + a.col_idx[e + kPrThreads]);
+          s2 += __ldcg(c_cur + a.col_idx[e + 2 * kPrThreads]);
+          s3 += __ldcg(c_cur + a.col_idx[e + 3 * kPrThreads]);
+        }
+        for (; e < b1; e += kPrThreads) s0 += __ldcg(c_cur + a.col_idx[e]);
+        float s = warp_sum((s0 + s1) + (s2 + s3));
+        if ((tid & 31) == 0) s_red[tid >> 5] = s;
+        __syncthreads();
+        if (tid == 0) {
+          float t = 0.f;
 #pragma unroll
-      for (int w = 0; w < kPrThreads / 32; ++w) t += s_red[w];
-      pr_finish_row(a, c, c_next_local, row, t);
+          for (int w = 0; w < kPrThreads / 32; ++w) t += s_red[w];
+          pr_finish_row(a, c, c_next_local, r, t);
+        }
+        __syncthreads();
+      }
     }
-    __syncthreads();
-  }
-
-  // ---- light rows: 8 lanes per row ---------------------------------------------------------------
-  const int sub = tid & (kGroup - 1);
-  const int64_t grp = ((int64_t)blockIdx.x * kPrThreads + tid) / kGroup;
-  const int64_t n_grp = (int64_t)gridDim.x * kPrThreads / kGroup;
-  for (int64_t row0 = 0; row0 < a.nv_local; row0 += n_grp) {
-    const int64_t row = row0 + grp;
-    const bool valid = row < a.nv_local;
-    int64_t e0 = 0, e1 = 0;
-    if (valid) { e0 = a.row_ptr[row]; e1 = a.row_ptr[row + 1]; }
-    const bool is_heavy = a.n_heavy > 0 && (e1 - e0) >= a.heavy_threshold;
-    float s = 0.f;
-    if (valid && !is_heavy)
-      for (int64_t e = e0 + sub; e < e1; e += kGroup) s += __ldcg(c_cur + a.col_idx[e]);
-#pragma unroll
-    for (int o = kGroup / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (valid && !is_heavy && sub == 0) pr_finish_row(a, c, c_next_local, row, s);
   }
 
   // ---- completion: last CTA tells every rank that this rank's slice of iteration `epoch` is in ----
@@ -144,18 +165,19 @@ extern "C" int dapb_pagerank_init(const DapbComm* comm, const float* inv_outdeg,
 }
 
 extern "C" int dapb_pagerank_step(const DapbComm* comm, const int64_t* row_ptr, const int32_t* col_idx,
-                                  const float* inv_outdeg, const int32_t* heavy, int32_t n_heavy,
-                                  int32_t heavy_threshold, int64_t nv_local, int64_t v0, int64_t V, float base,
+                                  const float* inv_outdeg, const int32_t* blocks, int32_t n_blocks,
+                                  int64_t nv_local, int64_t v0, int64_t V, float base,
                                   float damp, float* ranks_local, uint64_t c_off, uint32_t flag_base,
                                   uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t grid, void* stream) {
   DAPB_REQUIRE(comm && comm->world >= 1 && comm->world <= DAPB_MAX_RANKS, "pagerank_step: bad comm");
   DAPB_REQUIRE(epoch >= 1 && ticket != nullptr, "pagerank_step: epoch starts at 1, ticket required");
+  DAPB_REQUIRE(blocks != nullptr && n_blocks >= 0, "pagerank_step: row blocks required (see build_sharded_graph)");
   PrArgs a;
-  a.row_ptr = row_ptr; a.col_idx = col_idx; a.inv_outdeg = inv_outdeg; a.heavy = heavy;
-  a.n_heavy = heavy ? n_heavy : 0; a.heavy_threshold = heavy_threshold;
+  a.row_ptr = row_ptr; a.col_idx = col_idx; a.inv_outdeg = inv_outdeg; a.blocks = blocks; a.n_blocks = n_blocks;
   a.nv_local = nv_local; a.v0 = v0; a.V = V; a.base = base; a.damp = damp; a.ranks_local = ranks_local;
   a.c_off = c_off; a.flag_base = flag_base; a.epoch = epoch; a.ticket = ticket; a.wait_prev = wait_prev;
   if (grid <= 0) grid = dapb::sm_count() * 8;
+  if (grid > n_blocks) grid = n_blocks > 0 ? n_blocks : 1;
   pagerank_step_kernel<<<grid, kPrThreads, 0, (cudaStream_t)stream>>>(a, *comm);
   DAPB_LAUNCH_CHECK();
   return 0;

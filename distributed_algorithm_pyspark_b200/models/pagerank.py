@@ -35,12 +35,12 @@ class ShardedGraph:
     col_idx: torch.Tensor        # int32 [nnz_local] source ids
     inv_outdeg: torch.Tensor     # float32 [nv_local]
     outdeg_local: torch.Tensor   # int64 [nv_local]
-    heavy: Optional[torch.Tensor] = None
-    heavy_threshold: int = 2048
+    blocks: Optional[torch.Tensor] = None    # int32 [n_blocks + 1] row boundaries of ~block_nnz non-zeros each
+    block_nnz: int = 2048
 
 
 def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Optional[Dist] = None,
-                        heavy_threshold: int = 2048) -> ShardedGraph:
+                        block_nnz: int = 2048) -> ShardedGraph:
     """De-duplicate (ref pagerank.py:41) and build this rank's CSR(A^T) rows.  ``src``/``dst`` hold the FULL
     edge list on every rank (the generators are deterministic), int64 on the target device."""
     dist = dist or current()
@@ -59,13 +59,21 @@ def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Opti
     row_ptr[1:] = torch.cumsum(indeg, 0)
     od = outdeg[v0:v1]
     inv = torch.where(od > 0, 1.0 / od.clamp(min=1).to(torch.float32), torch.zeros((), device=src.device))
-    heavy = torch.nonzero(indeg >= heavy_threshold).squeeze(1).to(torch.int32)
-    if heavy.numel():
-        order = torch.argsort(indeg[heavy.long()], descending=True)
-        heavy = heavy[order].contiguous()
+    # work-balanced row blocks for the CSR-stream kernel: a row costs (in-degree + 1) units, block k starts at the
+    # first row whose cumulative cost is >= k * block_nnz, so a block holds <= block_nnz rows AND (unless it
+    # contains one very long row) <= block_nnz non-zeros -- the skewed R-MAT degrees are balanced by construction
+    nv = v1 - v0
+    nnz = int(row_ptr[-1].item())
+    cumw = (row_ptr[:-1] + torch.arange(nv, device=src.device, dtype=torch.int64)).contiguous()
+    n_blocks = max(1, (nnz + nv + block_nnz - 1) // block_nnz)
+    targets = torch.arange(n_blocks, device=src.device, dtype=torch.int64) * block_nnz
+    starts = torch.searchsorted(cumw, targets, right=False).clamp(max=nv)
+    if starts.numel():
+        starts[0] = 0
+    blocks = torch.cat([starts, torch.tensor([nv], device=src.device)]).to(torch.int32).contiguous()
     return ShardedGraph(V=V, n_sources=n_sources, n_edges=n_edges, v0=v0, v1=v1, row_ptr=row_ptr,
                         col_idx=s_loc.to(torch.int32).contiguous(), inv_outdeg=inv.contiguous(), outdeg_local=od,
-                        heavy=heavy if heavy.numel() else None, heavy_threshold=heavy_threshold)
+                        blocks=blocks, block_nnz=block_nnz)
 
 
 class ShardedPageRank:
@@ -127,10 +135,9 @@ class ShardedPageRank:
         g, cfg = self.g, self.cfg
         base, damp = cfg.q / self.n, 1.0 - cfg.q
         if self.backend == "fused":
-            heavy = g.heavy
             _native.check(self.lib.dapb_pagerank_step(
                 self.heap.comm_ref(), g.row_ptr.data_ptr(), g.col_idx.data_ptr(), g.inv_outdeg.data_ptr(),
-                _native.ptr(heavy), 0 if heavy is None else heavy.numel(), g.heavy_threshold, self.nv, g.v0, g.V,
+                g.blocks.data_ptr(), g.blocks.numel() - 1, self.nv, g.v0, g.V,
                 base, damp, self.ranks_local.data_ptr(), self.region.payload_off, self.region.flag_base,
                 self.region.next_epoch(), self.ticket.data_ptr(), 0 if self._first else 1, self.grid,
                 _native.stream_ptr()), "pagerank_step")

@@ -189,8 +189,8 @@ DAPB_API int dapb_kmeans_assign_tc_dbg(const void* X, int64_t n, int32_t d, cons
 DAPB_API int dapb_pagerank_init(const DapbComm* comm, const float* inv_outdeg, int64_t nv_local, int64_t v0,
                                 int64_t V, float r0, uint64_t c_off, void* stream);
 DAPB_API int dapb_pagerank_step(const DapbComm* comm, const int64_t* row_ptr, const int32_t* col_idx,
-                                const float* inv_outdeg, const int32_t* heavy, int32_t n_heavy,
-                                int32_t heavy_threshold, int64_t nv_local, int64_t v0, int64_t V, float base,
+                                const float* inv_outdeg, const int32_t* blocks, int32_t n_blocks,
+                                int64_t nv_local, int64_t v0, int64_t V, float base,
                                 float damp, float* ranks_local, uint64_t c_off, uint32_t flag_base,
                                 uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t grid, void* stream);
 

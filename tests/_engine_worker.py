@@ -73,7 +73,7 @@ def main():
     # ---- PageRank engine
     s, d = rmat_edges_np(12, 16, seed=3)
     src, dst = torch.as_tensor(s, device=dev), torch.as_tensor(d, device=dev)
-    g = build_sharded_graph(src, dst, 1 << 12, dist, heavy_threshold=64)
+    g = build_sharded_graph(src, dst, 1 << 12, dist, block_nnz=512)
     cfg = PageRankConfig(n_iterations=10)
     pa = ShardedPageRank(g, cfg, dist, backend="fused", heap=heap)
     pb = ShardedPageRank(g, cfg, dist, backend="nccl")

@@ -243,8 +243,8 @@ def test_pagerank_heavy_row_path(dist):
     V = 1 << 11
     cfg = PageRankConfig(n_iterations=5)
     outs = []
-    for thr in (1 << 30, 16):             # no heavy rows vs many heavy rows
-        g = build_sharded_graph(src, dst, V, dist, heavy_threshold=thr)
+    for thr in (2048, 16):                # default row blocks vs tiny blocks (long rows take the CTA-wide path)
+        g = build_sharded_graph(src, dst, V, dist, block_nnz=thr)
         pr = ShardedPageRank(g, cfg, dist, backend="fused")
         for _ in range(cfg.n_iterations):
             pr.step()
