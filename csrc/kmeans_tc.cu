@@ -7,10 +7,11 @@
 // accumulator lives in TMEM, the centroid operand holds -2c and ||c||^2 is added in the epilogue.
 //
 // Persistent, warp-specialised, one CTA per SM (512 threads):
-//   warp 0   TMA producer A : 128-row tiles of X (HBM -> smem, 128B swizzle), ring of 5 slots
-//   warp 3   TMA producer B : 128-centroid chunks of the prepared operand (L2 -> smem), 2 stages
-//   warp 1   MMA issuer     : for each super tile (4 row tiles) x each centroid chunk: 8 x tcgen05.mma
-//   warp 2   TMEM allocator (512 columns = 4 accumulator buffers of 128 columns), then producer of the ||c||^2 ring
+//   warp 0   three producer lanes: lane 0 TMA of 128-row tiles of X (HBM -> smem, 128B swizzle, ring of 5 slots),
+//            lane 1 TMA of 128-centroid chunks of the prepared operand (L2 -> smem, 2 stages), lane 2 ||c||^2 ring
+//   warps 1,3  MMA issuers : for each super tile (4 row tiles) x each centroid chunk: 8 x tcgen05.mma per row tile;
+//            warp 1 issues row tiles 0 and 2, warp 3 row tiles 1 and 3
+//   warp 2   TMEM allocator (512 columns = 4 accumulator buffers of 128 columns)
 //   warps 4-7 and 12-15  arg-min epilogue (row tiles 0-1 / 2-3 of the super tile) : tcgen05.ld (32 columns at a time, next load in flight while the current
 //              one is reduced) -> + ||c||^2 (smem ring fed by warp 2) -> value with the column-in-group index in its 5 low mantissa
 //              bits -> running min per row; a TMEM buffer is released as soon as it is in registers
@@ -113,7 +114,7 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     for (int i = 0; i < kASlots; ++i) {
       mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); mbar_init(&as_full[i], 4); mbar_init(&as_empty[i], 4);
     }
-    for (int i = 0; i < kBStages; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
+    for (int i = 0; i < kBStages; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 2); }   // two MMA issuers
     for (int i = 0; i < kTBufs; ++i) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], 4); }
     for (int i = 0; i < kCnStages; ++i) { mbar_init(&cn_full[i], 1); mbar_init(&cn_empty[i], 8); }
     fence_barrier_init();
@@ -124,9 +125,9 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
 
-  if (warp == 0) {
-    // ===================== TMA producer: X tiles =====================
-    if (lane == 0) {
+  if (warp == 0 && lane == 0) {
+    // ===================== TMA producer: X tiles (warp 0, lane 0) =====================
+    {
       prefetch_tensormap(&map_x);
       uint32_t g = 0;                                    // tiles loaded by this CTA so far
       for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
@@ -144,9 +145,9 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         }
       }
     }
-  } else if (warp == 3) {
-    // ===================== TMA producer: centroid chunks =====================
-    if (lane == 0) {
+  } else if (warp == 0 && lane == 1) {
+    // ===================== TMA producer: centroid chunks (warp 0, lane 1) =====================
+    {
       prefetch_tensormap(&map_c);
       uint32_t j = 0;
       for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
@@ -161,9 +162,9 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         }
       }
     }
-  } else if (warp == 2) {
-    // ===================== producer: ||c||^2 chunks for the arg-min warps =====================
-    if (lane == 0) {
+  } else if (warp == 0 && lane == 2) {
+    // ===================== producer: ||c||^2 chunks for the arg-min warps (warp 0, lane 2) =====================
+    {
       uint32_t j = 0;
       for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
         for (int c = 0; c < n_chunks; ++c, ++j) {
@@ -174,14 +175,16 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
+  } else if (warp == 1 || warp == 3) {
+    // ===================== MMA issuers: warp 1 takes row tiles 0 and 2 of every super tile, warp 3 tiles 1 and 3 =====================
+    // (one issuing thread spends ~600 cycles per accumulator on waits, descriptors and commits -- more than the
+    //  512 cycles the tensor core needs for it -- so two threads alternate)
     {
       constexpr uint32_t idesc = make_idesc_bf16(kTM, kNB, 0, 0);
       const uint64_t desc_tmpl = make_smem_desc_sw128(0, 16, 1024);
       const uint32_t a_base = smem_u32(smem + L::kAOff), b_base = smem_u32(smem + L::kBOff);
-      const bool leader = true;
-      uint32_t g0 = 0, j = 0, q = 0;                     // tile / chunk / accumulator counters
+      const int mma_id = warp == 1 ? 0 : 1;
+      uint32_t g0 = 0, j = 0, q0 = 0;                    // tiles / chunks / accumulators before this super tile
       // only lane 0 runs the loop: 32 lanes polling the mbarriers measurably slows the whole SM down (18.1 vs 8.9 ms)
       const int64_t n_super_mma = lane == 0 ? n_super : 0;
       for (int64_t s = blockIdx.x; s < n_super_mma; s += gridDim.x) {
@@ -190,8 +193,9 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         for (int c = 0; c < n_chunks; ++c, ++j) {
           const uint32_t st = j % kBStages;
           DAPB_T(pc0, mbar_wait(&b_full[st], (j / kBStages) & 1));
-          for (int t = 0; t < nt; ++t, ++q) {
+          for (int t = mma_id; t < nt; t += 2) {
             const uint32_t g = g0 + t, slot = g % kASlots;
+            const uint32_t q = q0 + (uint32_t)(c * nt + t);
             if (c == 0) DAPB_T(pc1, mbar_wait(&a_full[slot], (g / kASlots) & 1));
             const uint32_t buf = q % kTBufs;
             DAPB_T(pc2, mbar_wait(&t_empty[buf], ((q / kTBufs) & 1) ^ 1));
@@ -201,24 +205,23 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const uint64_t da0 = desc_tmpl | (uint64_t)(((a_base + slot * L::kATile) & 0x3FFFF) >> 4);
             const uint64_t db0 = desc_tmpl | (uint64_t)(((b_base + st * L::kBChunk) & 0x3FFFF) >> 4);
             const uint32_t d_tmem = tmem_base + buf * kNB;
-            if (leader) {
-              DAPB_T(pc3, {
+            DAPB_T(pc3, {
 #pragma unroll
-                for (int h = 0; h < L::kHalves; ++h)
+              for (int h = 0; h < L::kHalves; ++h)
 #pragma unroll
-                  for (int ks = 0; ks < 4; ++ks)
-                    umma_bf16(d_tmem, da0 + (uint64_t)((h * (kTM * 128) + ks * 32) >> 4),
-                              db0 + (uint64_t)((h * (kNB * 128) + ks * 32) >> 4), idesc, (h | ks) != 0);
-              });
-              DAPB_T(pc4, {
-                umma_commit(&t_full[buf]);
-                if (c == n_chunks - 1) umma_commit(&a_empty[slot]);   // tensor core is done reading this X tile
-                if (t == nt - 1) umma_commit(&b_empty[st]);           // ... and this centroid chunk
-              });
-            }
+                for (int ks = 0; ks < 4; ++ks)
+                  umma_bf16(d_tmem, da0 + (uint64_t)((h * (kTM * 128) + ks * 32) >> 4),
+                            db0 + (uint64_t)((h * (kNB * 128) + ks * 32) >> 4), idesc, (h | ks) != 0);
+            });
+            DAPB_T(pc4, {
+              umma_commit(&t_full[buf]);
+              if (c == n_chunks - 1) umma_commit(&a_empty[slot]);   // tensor core is done reading this X tile
+            });
           }
+          umma_commit(&b_empty[st]);                               // this issuer is done with the centroid chunk
         }
         g0 += nt;
+        q0 += (uint32_t)(n_chunks * nt);
       }
     }
   } else if ((warp >= 4 && warp < 8) || warp >= 12) {
