@@ -23,6 +23,7 @@ from ..oracle import spark_semantics as sp
 from ..oracle.algorithms import KMeansResult, kmeans_oracle
 from ..parallel.dist import Dist, current
 from ..parallel.partition import RowSharding
+from ..utils.trace import span
 
 _DT = {torch.float32: 0, torch.bfloat16: 1, torch.float64: 2}
 
@@ -91,6 +92,11 @@ class ShardedKMeans:
 
     def step(self):
         """One Lloyd iteration (ref k-means.py:55-71)."""
+        with span("kmeans.step"):
+            self._step()
+        self.iteration += 1
+
+    def _step(self):
         if self.backend == "fused":
             st = _native.stream_ptr()
             if self.tc is not None:
@@ -115,7 +121,6 @@ class ShardedKMeans:
             has = cnt > 0
             self.centers[has] = sums[has] / cnt[has][:, None]
             self.counts_out.copy_(cnt.to(torch.int32))
-        self.iteration += 1
 
     def _assign_torch(self) -> torch.Tensor:
         out = torch.empty(self.n, dtype=torch.int64, device=self.X.device)

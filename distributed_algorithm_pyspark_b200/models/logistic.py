@@ -28,6 +28,7 @@ from ..oracle import spark_semantics as sp
 from ..oracle.algorithms import LogisticInit, LogisticResult, logistic_oracle
 from ..parallel.dist import Dist, current
 from ..parallel.partition import RowSharding
+from ..utils.trace import span
 from ..utils.philox import bernoulli_threshold, philox_row_mask_np, philox_row_mask_torch
 
 
@@ -307,6 +308,11 @@ class ShardedLogisticEngine:
 
     def step(self, stream=None):
         """One outer iteration / communication round of ``cfg.algo`` (ref loop bodies cited above)."""
+        with span("logistic.step"):
+            self._step(stream)
+        self.t += 1
+
+    def _step(self, stream=None):
         cfg, t = self.cfg, self.t
         if self.backend == "nccl":
             self._step_nccl()
@@ -318,7 +324,6 @@ class ShardedLogisticEngine:
                 last = li == n_inner - 1
                 self._launch(_native.FIN_LOCAL_SYNC if last else _native.FIN_LOCAL, self.w_local, t,
                              reset=int(cfg.algo != "easgd"), stream=stream)
-        self.t += 1
 
     def evaluate(self, X_test: torch.Tensor, y_test: torch.Tensor) -> torch.Tensor:
         """Accuracy of the current global ``w`` on a (replicated) test set; stays on device."""

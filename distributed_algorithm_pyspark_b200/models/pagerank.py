@@ -21,6 +21,7 @@ from ..config import PageRankConfig
 from ..oracle.algorithms import pagerank_oracle
 from ..parallel.dist import Dist, current
 from ..parallel.partition import vertex_range
+from ..utils.trace import span
 
 
 @dataclass
@@ -132,6 +133,11 @@ class ShardedPageRank:
         return torch.cat([p[:b - a] for p, (a, b) in zip(parts, sizes)])
 
     def step(self):
+        with span("pagerank.step"):
+            self._step()
+        self.it += 1
+
+    def _step(self):
         g, cfg = self.g, self.cfg
         base, damp = cfg.q / self.n, 1.0 - cfg.q
         if self.backend == "fused":
@@ -150,7 +156,6 @@ class ShardedPageRank:
             r = torch.where(s > 0, base + damp * s, torch.zeros_like(s))
             self.ranks_local = r
             self.c = self._gather(r * self.inv)
-        self.it += 1
 
     def finish(self):
         """Make sure every rank's last pushes landed before buffers are reused (fused backend)."""
