@@ -34,6 +34,8 @@ def parse():
     ap.add_argument("--fraction", type=float, default=0.1)
     ap.add_argument("--no-extras", action="store_true", help="only the headline metric and its e2e number")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--lr-kernel", default="auto", choices=["auto", "cuda", "tc"],
+                    help="logistic step kernel: CUDA-core streaming kernel or the tcgen05 variant (auto = the faster one measured)")
     ap.add_argument("--e2e-steps", type=int, default=6)
     return ap.parse_args()
 
@@ -74,7 +76,8 @@ def bench_logistic(args, dist, algo, steps, warmup, backend, X, y, sampler=None)
     from distributed_algorithm_pyspark_b200.models.logistic import ShardedLogisticEngine
     cfg = LogisticConfig.for_algo(algo, eta=0.1, mini_batch_fraction=args.fraction, seed=0, sampler="philox",
                                   n_slices=dist.world)
-    eng = ShardedLogisticEngine(X, y, cfg, row_base=dist.rank * X.shape[0], dist=dist, backend=backend)
+    eng = ShardedLogisticEngine(X, y, cfg, row_base=dist.rank * X.shape[0], dist=dist, backend=backend,
+                                use_tc=(args.lr_kernel == "tc"))
     total = torch.zeros(1, dtype=torch.int64, device=X.device)
 
     def step():

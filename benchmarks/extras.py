@@ -81,7 +81,8 @@ def bench_pagerank(dist, backend, scale=24, edge_factor=16, iters=10, warmup=2):
     ms = _timed(dist, pr.step, iters, warmup)
     pr.finish()
     out = {"pagerank_gteps": g.n_edges / (ms / 1e3) / 1e9, "pagerank_ms_per_iter": ms, "pagerank_scale": scale,
-           "pagerank_edges_dedup": g.n_edges, "pagerank_row_blocks": int(g.blocks.numel() - 1)}
+           "pagerank_edges_dedup": g.n_edges, "pagerank_row_blocks": int(g.blocks.numel() - 1),
+           "pagerank_local_nnz": int(g.col_idx.numel()), "pagerank_local_vertices": int(g.v1 - g.v0)}
     del pr, g
     torch.cuda.empty_cache()
     return out

@@ -17,6 +17,7 @@
 
 #include "comm.cuh"
 #include "philox.cuh"
+#include "tc_common.cuh"
 
 using namespace dapb;
 
@@ -570,6 +571,342 @@ extern "C" int dapb_lr_step(const DapbLrStepArgs* args, const DapbComm* comm, vo
     }
   }
   return a.dtype == 1 ? launch_generic<__nv_bfloat16>(a, c, grid, s) : launch_generic<float>(a, c, grid, s);
+}
+
+// =================================================================================================
+// Tensor-core step kernel (bf16, D = 1024): forward z = Xw and backward g = X^T r as tcgen05.mma chains
+// =================================================================================================
+// The GEMV-shaped problem is mapped onto the tensor cores by padding N to 16 and spending the padding on
+// precision: the weight operand holds (bf16(w), bf16(w - bf16(w))) and the residual operand (bf16(r), bf16(r - bf16(r))),
+// so both products carry ~16 mantissa bits although every MMA input is bf16.
+//
+// A 128-row x 1024-feature tile is 256 KB and does not fit in shared memory, so it is streamed twice in slabs
+// of 128 features (32 KB): pass F (forward, K-major A) comes from HBM, pass B (backward, the same slabs read as
+// MN-major A) hits L2.  Sampled rows are not contiguous, so the slabs are gathered by loader warps
+// (16-byte LDG -> 128B-swizzled STS, then fence.proxy.async) instead of TMA boxes.  Roles per CTA (768 threads):
+//   warp 0      sampler: Philox Bernoulli decisions -> lists of 128 selected row indices (ring of 3)
+//   warp 1      MMA issuer, software-pipelined as F(0) F(1) B(0) F(2) B(1) ... so the sigmoid epilogue of tile t
+//               overlaps the forward MMAs of tile t+1
+//   warp 2      TMEM allocator (256 columns: 2 x 16 for z, 8 x 16 for the gradient blocks)
+//   warps 4-7   epilogue: tcgen05.ld z -> r = sigmoid(z) - y -> residual operand in swizzled smem; at the end
+//               tcgen05.ld of the gradient accumulators -> this CTA's partial row
+//   warps 8-23  two loader groups of 8 warps working on alternating slabs (64 KB in flight per SM)
+// The partial rows go through the same deterministic grid reduction + in-kernel peer all-reduce + optimiser
+// update (lr_finalize) as the CUDA-core kernel.
+namespace {
+
+constexpr int kTcThreads = 768;
+constexpr int kTcD = 1024;
+constexpr int kTcTM = 128;                 // rows per tile
+constexpr int kTcFB = 128;                 // features per slab
+constexpr int kTcSlabs = kTcD / kTcFB;     // 8 slabs per pass
+constexpr int kTcRing = 5;                 // slab ring slots (32 KB each)
+constexpr int kTcLists = 3;
+constexpr uint32_t kTcSlabBytes = kTcTM * kTcFB * 2;                       // 32 KB
+constexpr uint32_t kTcWOff = kTcRing * kTcSlabBytes;                       // weight operand: 16 x [16 rows x 128 B]
+constexpr uint32_t kTcWBytes = (kTcD / 64) * 16 * 128;                     // 32 KB
+constexpr uint32_t kTcROff = kTcWOff + kTcWBytes;                          // residual operand: 2 x (2 x [16 x 128 B])
+constexpr uint32_t kTcRBytes = 2 * 16 * 128;                               // 4 KB per buffer
+constexpr uint32_t kTcListOff = kTcROff + 2 * kTcRBytes;                   // 3 x (n_valid, pad[3], rows[128])
+constexpr uint32_t kTcListBytes = (4 + kTcTM) * 4;
+constexpr uint32_t kTcBarOff = kTcListOff + kTcLists * kTcListBytes;
+constexpr int kTcNumBars = 2 * kTcRing + 2 * kTcLists + 2 + 2 + 2 + 2 + 1;
+constexpr uint32_t kTcTmemOff = kTcBarOff + kTcNumBars * 8;
+constexpr uint32_t kTcTotal = kTcTmemOff + 16;
+
+using namespace dapb::tc;
+
+__global__ void __launch_bounds__(kTcThreads, 1) lr_tc_kernel(DapbLrStepArgs a, DapbComm c, uint32_t smem_bytes) {
+  extern __shared__ __align__(1024) uint8_t tc_smem_raw[];
+  const uint32_t pad = (1024u - (smem_u32(tc_smem_raw) & 1023u)) & 1023u;
+  uint8_t* smem = tc_smem_raw + pad;
+  if (pad + kTcTotal > smem_bytes) __trap();
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kTcBarOff);
+  uint64_t* slot_full = bars;                       // [ring]  8 arrivals (one loader group)
+  uint64_t* slot_empty = slot_full + kTcRing;       // [ring]  1 (MMA commit)
+  uint64_t* list_full = slot_empty + kTcRing;       // [lists] 1 (sampler)
+  uint64_t* list_empty = list_full + kTcLists;      // [lists] 20 (16 loader warps + 4 epilogue warps)
+  uint64_t* z_full = list_empty + kTcLists;         // [2] 1 (MMA commit)
+  uint64_t* z_empty = z_full + 2;                   // [2] 4 (epilogue warps)
+  uint64_t* r_full = z_empty + 2;                   // [2] 4 (epilogue warps)
+  uint64_t* r_empty = r_full + 2;                   // [2] 1 (MMA commit)
+  uint64_t* g_done = r_empty + 2;                   // 1
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(smem + kTcTmemOff);
+  __shared__ bool s_last;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
+
+  if (tid == 0) {
+    for (int i = 0; i < kTcRing; ++i) { mbar_init(&slot_full[i], 8); mbar_init(&slot_empty[i], 1); }
+    for (int i = 0; i < kTcLists; ++i) { mbar_init(&list_full[i], 1); mbar_init(&list_empty[i], 20); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&z_full[i], 1); mbar_init(&z_empty[i], 4); mbar_init(&r_full[i], 4); mbar_init(&r_empty[i], 1); }
+    mbar_init(g_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) { tmem_alloc(tmem_holder, 256); tmem_relinquish(); }
+  // weight operand (K-major, 128B swizzle): row 0 = bf16(w), row 1 = bf16(w - bf16(w)), rows 2..15 = 0
+  for (int i = tid; i < (int)(kTcWBytes + 2 * kTcRBytes) / 16; i += kTcThreads)
+    reinterpret_cast<uint4*>(smem + kTcWOff)[i] = make_uint4(0u, 0u, 0u, 0u);
+  __syncthreads();
+  for (int k = tid; k < kTcD; k += kTcThreads) {
+    const float wv = a.w_fwd[k];
+    const __nv_bfloat16 hi = __float2bfloat16(wv);
+    const __nv_bfloat16 lo = __float2bfloat16(wv - __bfloat162float(hi));
+    const int slab = k >> 6, kk = k & 63, chunk = kk >> 3, within = (kk & 7) * 2;
+    uint8_t* base = smem + kTcWOff + slab * 2048;
+    *reinterpret_cast<__nv_bfloat16*>(base + 0 * 128 + ((chunk ^ 0) << 4) + within) = hi;
+    *reinterpret_cast<__nv_bfloat16*>(base + 1 * 128 + ((chunk ^ 1) << 4) + within) = lo;
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+  const uint32_t tmem_z = tmem_base, tmem_g = tmem_base + 32;
+  auto list_ptr = [&](int t) { return reinterpret_cast<int*>(smem + kTcListOff + (t % kTcLists) * kTcListBytes); };
+
+  if (warp == 0) {
+    // ===================== sampler =====================
+    const int64_t n_chunks = (a.n_rows + 31) >> 5;
+    const bool all_rows = a.mask == nullptr && a.threshold24 >= (1u << 24);
+    int t = 0, fill = 0, kept_total = 0;
+    mbar_wait(&list_empty[0], 1);                        // fresh barrier: passes immediately
+    int* lst = list_ptr(0);
+    for (int64_t ch = blockIdx.x; ch < n_chunks; ch += gridDim.x) {
+      const int64_t row = (ch << 5) + lane;
+      bool keep = row < a.n_rows;
+      if (keep && !all_rows)
+        keep = a.mask ? (a.mask[row] != 0)
+                      : philox_keep_row((uint64_t)(a.row_base + row), a.iteration, a.seed, a.threshold24);
+      unsigned bits = __ballot_sync(0xffffffffu, keep);
+      kept_total += __popc(bits);
+      while (bits) {
+        const int avail = __popc(bits), take = min(avail, kTcTM - fill);
+        const int rank = __popc(bits & ((1u << lane) - 1));
+        if (((bits >> lane) & 1u) && rank < take) lst[4 + fill + rank] = (int)row;
+        fill += take;
+        if (take == avail) bits = 0;
+        else for (int i = 0; i < take; ++i) bits &= bits - 1;        // drop the `take` lowest set bits (tile boundary)
+        if (fill == kTcTM) {
+          if (lane == 0) lst[0] = kTcTM;
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&list_full[t % kTcLists]);
+          ++t; fill = 0;
+          mbar_wait(&list_empty[t % kTcLists], ((t / kTcLists) & 1) ^ 1);
+          lst = list_ptr(t);
+        }
+      }
+    }
+    if (fill > 0) {                                       // ragged last tile: pad with "no row"
+      for (int i = fill + lane; i < kTcTM; i += 32) lst[4 + i] = -1;
+      if (lane == 0) lst[0] = fill;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&list_full[t % kTcLists]);
+      ++t;
+      mbar_wait(&list_empty[t % kTcLists], ((t / kTcLists) & 1) ^ 1);
+      lst = list_ptr(t);
+    }
+    if (lane == 0) lst[0] = -1;                           // terminator
+    __syncwarp();
+    if (lane == 0) { mbar_arrive(&list_full[t % kTcLists]); a.counts[blockIdx.x] = kept_total; }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc_f = make_idesc_bf16(kTcTM, 16, 0, 0);           // A K-major, B K-major
+      constexpr uint32_t idesc_b = make_idesc_bf16(kTcFB, 16, 1, 0);           // A MN-major (X^T), B K-major
+      const uint64_t tmpl_k = make_smem_desc_sw128(0, 16, 1024);
+      const uint64_t tmpl_mn = make_smem_desc_sw128(0, kTcTM * 128, 1024);     // LBO = next 64-feature half
+      const uint32_t ring = smem_u32(smem), wop = smem_u32(smem + kTcWOff), rop = smem_u32(smem + kTcROff);
+      uint32_t n = 0;                                                          // slab sequence counter
+      auto fwd = [&](int t) {
+        const int zb = t & 1;
+        mbar_wait(&z_empty[zb], ((t >> 1) & 1) ^ 1);
+        tc_fence_after();
+        for (int fb = 0; fb < kTcSlabs; ++fb, ++n) {
+          const uint32_t slot = n % kTcRing;
+          mbar_wait(&slot_full[slot], (n / kTcRing) & 1);
+          tc_fence_after();
+          const uint32_t sa = ring + slot * kTcSlabBytes;
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+              const uint64_t da = tmpl_k | (uint64_t)(((sa + h * (kTcTM * 128) + ks * 32) & 0x3FFFF) >> 4);
+              const uint64_t db = tmpl_k | (uint64_t)(((wop + (fb * 2 + h) * 2048 + ks * 32) & 0x3FFFF) >> 4);
+              umma_bf16(tmem_z + zb * 16, da, db, idesc_f, (fb | h | ks) != 0);
+            }
+          umma_commit(&slot_empty[slot]);
+        }
+        umma_commit(&z_full[zb]);
+      };
+      auto bwd = [&](int t) {
+        const int rb = t & 1;
+        mbar_wait(&r_full[rb], (t >> 1) & 1);
+        tc_fence_after();
+        for (int fb = 0; fb < kTcSlabs; ++fb, ++n) {
+          const uint32_t slot = n % kTcRing;
+          mbar_wait(&slot_full[slot], (n / kTcRing) & 1);
+          tc_fence_after();
+          const uint32_t sa = ring + slot * kTcSlabBytes;
+#pragma unroll
+          for (int kr = 0; kr < 8; ++kr) {                                    // 16 rows per MMA
+            const uint64_t da = tmpl_mn | (uint64_t)(((sa + kr * 2048) & 0x3FFFF) >> 4);
+            const uint64_t db = tmpl_k | (uint64_t)(((rop + rb * kTcRBytes + (kr >> 2) * 2048 + (kr & 3) * 32) & 0x3FFFF) >> 4);
+            umma_bf16(tmem_g + fb * 16, da, db, idesc_b, (t | kr) != 0);
+          }
+          umma_commit(&slot_empty[slot]);
+        }
+        umma_commit(&r_empty[rb]);
+      };
+      mbar_wait(&list_full[0], 0);
+      if (list_ptr(0)[0] >= 0) {
+        fwd(0);
+        for (int t = 1;; ++t) {
+          mbar_wait(&list_full[t % kTcLists], (t / kTcLists) & 1);
+          const int nv = list_ptr(t)[0];
+          if (nv >= 0) fwd(t);
+          bwd(t - 1);
+          if (nv < 0) break;
+        }
+      }
+      umma_commit(g_done);
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ===================== epilogue =====================
+    const int qd = warp & 3, row_in_tile = qd * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(qd * 32) << 16;
+    int n_tiles = 0;
+    for (int t = 0;; ++t) {
+      mbar_wait(&list_full[t % kTcLists], (t / kTcLists) & 1);
+      const int* lst = list_ptr(t);
+      if (lst[0] < 0) break;
+      n_tiles = t + 1;
+      const int row = lst[4 + row_in_tile];
+      const float yv = row >= 0 ? a.y[row] : 0.f;
+      const int zb = t & 1;
+      mbar_wait(&z_full[zb], (t >> 1) & 1);
+      tc_fence_after();
+      uint32_t v0, v1;
+      asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(v0), "=r"(v1) : "r"(tmem_z + lane_addr + zb * 16) : "memory");
+      tmem_ld_wait();
+      tc_fence_before();
+      const float z = __uint_as_float(v0) + __uint_as_float(v1);
+      const float r = row >= 0 ? sigmoid_ref(z, a.eps) - yv : 0.f;                 // ref ssgd.py:33
+      const __nv_bfloat16 hi = __float2bfloat16(r);
+      const __nv_bfloat16 lo = __float2bfloat16(r - __bfloat162float(hi));
+      mbar_wait(&r_empty[zb], ((t >> 1) & 1) ^ 1);
+      {
+        const int slab = row_in_tile >> 6, kk = row_in_tile & 63, chunk = kk >> 3, within = (kk & 7) * 2;
+        uint8_t* base = smem + kTcROff + zb * kTcRBytes + slab * 2048;
+        *reinterpret_cast<__nv_bfloat16*>(base + 0 * 128 + ((chunk ^ 0) << 4) + within) = hi;
+        *reinterpret_cast<__nv_bfloat16*>(base + 1 * 128 + ((chunk ^ 1) << 4) + within) = lo;
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) { mbar_arrive(&r_full[zb]); mbar_arrive(&z_empty[zb]); mbar_arrive(&list_empty[t % kTcLists]); }
+    }
+    // gradient accumulators -> this CTA's partial row (column 0 = hi part, column 1 = lo part)
+    mbar_wait(g_done, 0);
+    tc_fence_after();
+    float* prow = a.partials + (int64_t)blockIdx.x * kTcD;
+    for (int fb = 0; fb < kTcSlabs; ++fb) {
+      float g = 0.f;
+      if (n_tiles > 0) {
+        uint32_t v0, v1;
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(v0), "=r"(v1) : "r"(tmem_g + lane_addr + fb * 16) : "memory");
+        tmem_ld_wait();
+        g = __uint_as_float(v0) + __uint_as_float(v1);
+      }
+      prow[fb * kTcFB + row_in_tile] = g;
+    }
+    tc_fence_before();
+  } else if (warp >= 8) {
+    // ===================== loaders: gather rows -> 128B-swizzled slabs =====================
+    const int grp = (warp - 8) >> 3;                       // two groups of 8 warps, alternating slabs
+    const int j = ((warp - 8) & 7) * 32 + lane;            // 0..255 inside the group
+    const int cc = j & 15, r_off = j >> 4;                 // 16-byte chunk of the 256-byte row segment, first row
+    const int h = cc >> 3, c8 = cc & 7;
+    const char* Xb = reinterpret_cast<const char*>(a.X);
+    uint32_t n = 0;
+    auto phase = [&](int t) {
+      const int* lst = list_ptr(t);
+      int rows[8];
+#pragma unroll
+      for (int it = 0; it < 8; ++it) rows[it] = lst[4 + r_off + 16 * it];
+      for (int fb = 0; fb < kTcSlabs; ++fb, ++n) {
+        if ((int)(n & 1) != grp) continue;
+        const uint32_t slot = n % kTcRing;
+        mbar_wait(&slot_empty[slot], ((n / kTcRing) & 1) ^ 1);
+        uint4 v[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it)
+          v[it] = rows[it] >= 0 ? ld_stream_16(Xb + (int64_t)rows[it] * (kTcD * 2) + fb * (kTcFB * 2) + cc * 16)
+                                : make_uint4(0u, 0u, 0u, 0u);
+        uint8_t* dst = smem + slot * kTcSlabBytes + h * (kTcTM * 128);
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const int i = r_off + 16 * it;
+          *reinterpret_cast<uint4*>(dst + i * 128 + ((c8 ^ (i & 7)) << 4)) = v[it];
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&slot_full[slot]);
+      }
+    };
+    mbar_wait(&list_full[0], 0);
+    if (list_ptr(0)[0] >= 0) {
+      phase(0);
+      for (int t = 1;; ++t) {
+        mbar_wait(&list_full[t % kTcLists], (t / kTcLists) & 1);
+        const int nv = list_ptr(t)[0];
+        if (nv >= 0) phase(t);
+        phase(t - 1);                                      // backward pass of the previous tile (L2 hits)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&list_empty[(t - 1) % kTcLists]);
+        if (nv < 0) break;
+      }
+    }
+  }
+
+  __threadfence();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, 256);
+  if (tid == 0) {
+    unsigned tk = atomicAdd(a.ticket, 1u);
+    s_last = (tk == gridDim.x - 1);
+    if (s_last) *a.ticket = 0;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  lr_finalize(a, c, reinterpret_cast<float*>(smem));
+}
+
+}  // namespace
+
+// Tensor-core variant of dapb_lr_step: same arguments and semantics, bf16 rows with D == 1024 only.
+extern "C" int dapb_lr_step_tc(const DapbLrStepArgs* args, const DapbComm* comm, void* stream) {
+  DAPB_REQUIRE(args && comm, "lr_step_tc: null argument");
+  DapbLrStepArgs a = *args;
+  DapbComm c = *comm;
+  DAPB_REQUIRE(a.dtype == 1 && a.D == kTcD, "lr_step_tc: needs bf16 rows with D == 1024 (got dtype %d, D %d)", a.dtype, a.D);
+  DAPB_REQUIRE((reinterpret_cast<uintptr_t>(a.X) & 15) == 0, "lr_step_tc: X must be 16-byte aligned");
+  DAPB_REQUIRE(a.n_rows < (1ll << 31), "lr_step_tc: more than 2^31 rows per shard");
+  DAPB_REQUIRE(a.fin >= DAPB_LR_FIN_GRAD_ONLY && a.fin <= DAPB_LR_FIN_LOCAL_SYNC, "lr_step_tc: bad fin");
+  DAPB_REQUIRE(a.partials && a.counts && a.ticket && a.w_fwd, "lr_step_tc: missing scratch / weights");
+  if ((a.fin == DAPB_LR_FIN_SSGD || a.fin == DAPB_LR_FIN_LOCAL_SYNC) && c.world > 1) {
+    DAPB_REQUIRE(a.epoch >= 1, "lr_step_tc: epoch starts at 1");
+    uint64_t need = DAPB_FLAG_BYTES + a.payload_off + (uint64_t)2 * c.world * ((a.D + 2 + 3) & ~3) * sizeof(float);
+    DAPB_REQUIRE(need <= c.heap_bytes, "lr_step_tc: heap too small");
+  }
+  int grid = a.grid > 0 ? a.grid : dapb::sm_count();
+  a.grid = grid;
+  const uint32_t smem = kTcTotal + 1024;
+  DAPB_CUDA_CHECK(cudaFuncSetAttribute(lr_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  lr_tc_kernel<<<grid, kTcThreads, smem, (cudaStream_t)stream>>>(a, c, smem);
+  DAPB_LAUNCH_CHECK();
+  return 0;
 }
 
 // ---------------------------------------------------------------------------------------------

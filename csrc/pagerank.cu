@@ -38,6 +38,7 @@ struct PrArgs {
   uint64_t epoch;           // iteration number, starts at 1
   uint32_t* ticket;
   int32_t wait_prev;        // wait for epoch-1 from every rank before reading
+  int32_t skip_empty;       // rows without in-edges already hold 0 in BOTH buffers (from the 3rd iteration on)
 };
 
 __device__ __forceinline__ void pr_finish_row(const PrArgs& a, const DapbComm& c, float* c_next_local,
@@ -91,6 +92,7 @@ __global__ void __launch_bounds__(kPrThreads) pagerank_step_kernel(PrArgs a, Dap
       __syncthreads();
       for (int r = r0 + tid; r < r1; r += kPrThreads) {
         const int b0 = (int)(a.row_ptr[r] - e0), b1 = (int)(a.row_ptr[r + 1] - e0);
+        if (b1 == b0 && a.skip_empty) continue;          // rank and contribution stay 0: nothing to store or push
         float s = 0.f;
         for (int j = b0; j < b1; ++j) s += vals[j];
         pr_finish_row(a, c, c_next_local, r, s);
@@ -168,14 +170,15 @@ extern "C" int dapb_pagerank_step(const DapbComm* comm, const int64_t* row_ptr, 
                                   const float* inv_outdeg, const int32_t* blocks, int32_t n_blocks,
                                   int64_t nv_local, int64_t v0, int64_t V, float base,
                                   float damp, float* ranks_local, uint64_t c_off, uint32_t flag_base,
-                                  uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t grid, void* stream) {
+                                  uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t skip_empty,
+                                  int32_t grid, void* stream) {
   DAPB_REQUIRE(comm && comm->world >= 1 && comm->world <= DAPB_MAX_RANKS, "pagerank_step: bad comm");
   DAPB_REQUIRE(epoch >= 1 && ticket != nullptr, "pagerank_step: epoch starts at 1, ticket required");
   DAPB_REQUIRE(blocks != nullptr && n_blocks >= 0, "pagerank_step: row blocks required (see build_sharded_graph)");
   PrArgs a;
   a.row_ptr = row_ptr; a.col_idx = col_idx; a.inv_outdeg = inv_outdeg; a.blocks = blocks; a.n_blocks = n_blocks;
   a.nv_local = nv_local; a.v0 = v0; a.V = V; a.base = base; a.damp = damp; a.ranks_local = ranks_local;
-  a.c_off = c_off; a.flag_base = flag_base; a.epoch = epoch; a.ticket = ticket; a.wait_prev = wait_prev;
+  a.c_off = c_off; a.flag_base = flag_base; a.epoch = epoch; a.ticket = ticket; a.wait_prev = wait_prev; a.skip_empty = skip_empty;
   if (grid <= 0) grid = dapb::sm_count() * 8;
   if (grid > n_blocks) grid = n_blocks > 0 ? n_blocks : 1;
   pagerank_step_kernel<<<grid, kPrThreads, 0, (cudaStream_t)stream>>>(a, *comm);

@@ -86,6 +86,7 @@ def _declare(lib: C.CDLL):
         "dapb_lr_parity_run": (C.c_int, [P(DapbLrParityArgs), P(DapbComm), vp]),
         "dapb_lr_parity_payload_bytes": (u64, [i32, i32]),
         "dapb_lr_step": (C.c_int, [P(DapbLrStepArgs), P(DapbComm), vp]),
+        "dapb_lr_step_tc": (C.c_int, [P(DapbLrStepArgs), P(DapbComm), vp]),
         "dapb_lr_eval": (C.c_int, [vp, vp, i64, i32, i32, vp, f32, vp, vp, vp]),
         "dapb_mc_pi": (C.c_int, [u64, u64, u64, vp, vp]),
         "dapb_kmeans_assign": (C.c_int, [vp, i64, i32, i32, vp, i32, vp, vp, vp, vp]),
@@ -96,7 +97,7 @@ def _declare(lib: C.CDLL):
         "dapb_kmeans_assign_tc_dbg": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, vp, vp, i32, vp, vp]),
         "dapb_pagerank_init": (C.c_int, [P(DapbComm), vp, i64, i64, i64, f32, u64, vp]),
         "dapb_pagerank_step": (C.c_int, [P(DapbComm), vp, vp, vp, vp, i32, i64, i64, i64, f32, f32, vp,
-                                         u64, u32, u64, vp, i32, i32, vp]),
+                                         u64, u32, u64, vp, i32, i32, i32, vp]),
         "dapb_tc_seed": (C.c_int, [vp, i64, vp, u64, vp, vp, i32, i32, vp]),
         "dapb_tc_expand": (C.c_int, [P(DapbComm), vp, vp, vp, i64, vp, u64, vp, vp, u64, u64, vp]),
         "dapb_tc_exchange": (C.c_int, [P(DapbComm), vp, u64, u64, u32, u64, vp]),

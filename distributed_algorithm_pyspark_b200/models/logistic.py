@@ -249,7 +249,7 @@ class ShardedLogisticEngine:
 
     def __init__(self, X: torch.Tensor, y: torch.Tensor, cfg: LogisticConfig, row_base: int = 0,
                  dist: Optional[Dist] = None, backend: str = "fused", w0: Optional[torch.Tensor] = None,
-                 grid: int = 0, heap=None):
+                 grid: int = 0, heap=None, use_tc: bool = False):
         self.dist = dist or current()
         self.cfg, self.backend = cfg, backend
         assert X.dim() == 2 and X.is_contiguous() and X.dtype in _DTYPE_ID
@@ -272,7 +272,9 @@ class ShardedLogisticEngine:
             self.lib = _native.load()
             self.heap = heap or default_heap()
             sms = torch.cuda.get_device_properties(dev).multi_processor_count
-            self.grid = grid or 2 * sms
+            # tensor-core variant (csrc/lr.cu::lr_tc_kernel): bf16 rows with D == 1024, one CTA per SM
+            self.use_tc = bool(use_tc) and X.dtype == torch.bfloat16 and self.D == 1024
+            self.grid = grid or (sms if self.use_tc else 2 * sms)
             self.partials = torch.empty(self.grid, self.D, dtype=torch.float32, device=dev)
             self.counts = torch.zeros(self.grid, dtype=torch.int32, device=dev)
             self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -304,7 +306,8 @@ class ShardedLogisticEngine:
         a.fin, a.w_fwd, a.iteration, a.reset_replica = fin, w_fwd.data_ptr(), iteration, reset
         if fin in (_native.FIN_SSGD, _native.FIN_LOCAL_SYNC):
             a.epoch = self.region.next_epoch()
-        _native.check(self.lib.dapb_lr_step(C.byref(a), self.heap.comm_ref(), _native.stream_ptr(stream)), "lr_step")
+        fn = self.lib.dapb_lr_step_tc if self.use_tc else self.lib.dapb_lr_step
+        _native.check(fn(C.byref(a), self.heap.comm_ref(), _native.stream_ptr(stream)), "lr_step")
 
     def step(self, stream=None):
         """One outer iteration / communication round of ``cfg.algo`` (ref loop bodies cited above)."""

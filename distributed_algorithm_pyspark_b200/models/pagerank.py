@@ -32,6 +32,7 @@ class ShardedGraph:
     n_edges: int                 # global, after de-duplication
     v0: int
     v1: int
+    bounds: tuple                # vertex-range boundaries of every rank (len world + 1), nnz-balanced
     row_ptr: torch.Tensor        # int64 [nv_local + 1]
     col_idx: torch.Tensor        # int32 [nnz_local] source ids
     inv_outdeg: torch.Tensor     # float32 [nv_local]
@@ -40,8 +41,24 @@ class ShardedGraph:
     block_nnz: int = 2048
 
 
+def balanced_vertex_bounds(indeg_all: torch.Tensor, world: int, vertex_cost: int = 8):
+    """Contiguous destination-vertex ranges with (almost) equal numbers of in-edges AND vertices per rank: the cost of
+    a vertex is in-degree + 1 (+ vertex_cost if it has in-edges: its new contribution is pushed to every peer each
+    iteration).  R-MAT graphs concentrate edges on low vertex ids, so equal-size ranges would give
+    rank 0 most of the work."""
+    V = indeg_all.numel()
+    cost = torch.cumsum(indeg_all + vertex_cost * (indeg_all > 0) + 1, 0)
+    total = int(cost[-1].item())
+    targets = torch.tensor([(total * r) // world for r in range(1, world)], device=indeg_all.device, dtype=cost.dtype)
+    cuts = torch.searchsorted(cost, targets, right=False).tolist() if world > 1 else []
+    b = [0] + [min(int(c) + 1, V) for c in cuts] + [V]
+    for i in range(1, len(b)):
+        b[i] = max(b[i], b[i - 1])
+    return tuple(b)
+
+
 def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Optional[Dist] = None,
-                        block_nnz: int = 2048) -> ShardedGraph:
+                        block_nnz: int = 2048, balance: bool = True) -> ShardedGraph:
     """De-duplicate (ref pagerank.py:41) and build this rank's CSR(A^T) rows.  ``src``/``dst`` hold the FULL
     edge list on every rank (the generators are deterministic), int64 on the target device."""
     dist = dist or current()
@@ -51,7 +68,11 @@ def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Opti
     n_edges = int(key.numel())
     outdeg = torch.bincount(s_all, minlength=V)
     n_sources = int((outdeg > 0).sum().item())
-    v0, v1 = vertex_range(V, dist.rank, dist.world)
+    if balance and dist.world > 1:
+        bounds = balanced_vertex_bounds(torch.bincount(d_all, minlength=V), dist.world)
+    else:
+        bounds = tuple(vertex_range(V, r, dist.world)[0] for r in range(dist.world)) + (V,)
+    v0, v1 = bounds[dist.rank], bounds[dist.rank + 1]
     lo = int(torch.searchsorted(d_all, torch.tensor([v0], device=d_all.device)).item())
     hi = int(torch.searchsorted(d_all, torch.tensor([v1], device=d_all.device)).item())
     d_loc, s_loc = d_all[lo:hi] - v0, s_all[lo:hi]
@@ -72,7 +93,7 @@ def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Opti
     if starts.numel():
         starts[0] = 0
     blocks = torch.cat([starts, torch.tensor([nv], device=src.device)]).to(torch.int32).contiguous()
-    return ShardedGraph(V=V, n_sources=n_sources, n_edges=n_edges, v0=v0, v1=v1, row_ptr=row_ptr,
+    return ShardedGraph(V=V, n_sources=n_sources, n_edges=n_edges, v0=v0, v1=v1, bounds=bounds, row_ptr=row_ptr,
                         col_idx=s_loc.to(torch.int32).contiguous(), inv_outdeg=inv.contiguous(), outdeg_local=od,
                         blocks=blocks, block_nnz=block_nnz)
 
@@ -91,6 +112,8 @@ class ShardedPageRank:
         self.n = max(graph.n_sources, 1)
         self.grid = grid
         self.it = 0
+        import os
+        self.skip_empty = os.environ.get("DAPB_PR_NOSKIP") is None
         if backend == "fused":
             from ..parallel.symm import default_heap
             self.lib = _native.load()
@@ -125,7 +148,7 @@ class ShardedPageRank:
     def _gather(self, loc: torch.Tensor) -> torch.Tensor:
         if self.dist.world == 1:
             return loc.clone()
-        sizes = [vertex_range(self.g.V, r, self.dist.world) for r in range(self.dist.world)]
+        sizes = [(self.g.bounds[r], self.g.bounds[r + 1]) for r in range(self.dist.world)]
         m = max(b - a for a, b in sizes)
         pad = torch.zeros(m, dtype=loc.dtype, device=loc.device)
         pad[:loc.numel()] = loc
@@ -145,7 +168,7 @@ class ShardedPageRank:
                 self.heap.comm_ref(), g.row_ptr.data_ptr(), g.col_idx.data_ptr(), g.inv_outdeg.data_ptr(),
                 g.blocks.data_ptr(), g.blocks.numel() - 1, self.nv, g.v0, g.V,
                 base, damp, self.ranks_local.data_ptr(), self.region.payload_off, self.region.flag_base,
-                self.region.next_epoch(), self.ticket.data_ptr(), 0 if self._first else 1, self.grid,
+                self.region.next_epoch(), self.ticket.data_ptr(), 0 if self._first else 1, int(self.it >= 2 and self.skip_empty), self.grid,
                 _native.stream_ptr()), "pagerank_step")
             self._first = False
         else:

@@ -131,6 +131,9 @@ typedef struct DapbLrStepArgs {
   uint64_t epoch;           /* strictly increasing per call on this flag_base */
 } DapbLrStepArgs;
 DAPB_API int dapb_lr_step(const DapbLrStepArgs* args, const DapbComm* comm, void* stream);
+/* Tensor-core variant (tcgen05.mma forward K-major + backward MN-major, TMEM accumulators, hi/lo bf16 split of w
+ * and of the residual): bf16 rows, D == 1024, grid defaults to one CTA per SM (partials must hold `grid` rows). */
+DAPB_API int dapb_lr_step_tc(const DapbLrStepArgs* args, const DapbComm* comm, void* stream);
 /* Test-set accuracy with the reference's 0.5 threshold (ref ssgd.py:107-110). acc_out: [1] float. */
 DAPB_API int dapb_lr_eval(const void* X, const float* y, int64_t n_rows, int32_t D, int32_t dtype,
                  const float* w, float eps, float* acc_out, uint32_t* scratch2, void* stream);
@@ -185,14 +188,16 @@ DAPB_API int dapb_kmeans_assign_tc_dbg(const void* X, int64_t n, int32_t d, cons
 /* ------------------------------------------------------------------ F4 PageRank -----------
  * ref: graph_computation/pagerank.py:21-25,44-57.  Contribution vector [2][V] float lives in the
  * symmetric heap at c_off; iteration `epoch` reads parity (epoch-1)&1 and pushes into parity epoch&1
- * on every rank.  Host must barrier between dapb_pagerank_init and the first step (wait_prev = 0). */
+ * on every rank.  Host must barrier between dapb_pagerank_init and the first step (wait_prev = 0).
+ * skip_empty = 1 (allowed from the 3rd step after init) skips rows without in-edges: both buffers already hold 0. */
 DAPB_API int dapb_pagerank_init(const DapbComm* comm, const float* inv_outdeg, int64_t nv_local, int64_t v0,
                                 int64_t V, float r0, uint64_t c_off, void* stream);
 DAPB_API int dapb_pagerank_step(const DapbComm* comm, const int64_t* row_ptr, const int32_t* col_idx,
                                 const float* inv_outdeg, const int32_t* blocks, int32_t n_blocks,
                                 int64_t nv_local, int64_t v0, int64_t V, float base,
                                 float damp, float* ranks_local, uint64_t c_off, uint32_t flag_base,
-                                uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t grid, void* stream);
+                                uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t skip_empty,
+                                int32_t grid, void* stream);
 
 /* ------------------------------------------------------------------ F6 transitive closure --
  * ref: graph_computation/transitive_closure.py:27-40.  Pairs are packed (x << 32 | z); the hash set

@@ -61,10 +61,50 @@ def gram(n, P, splits):
             "sym": float((G1 - G1.T).abs().max().item()) / scale}
 
 
+def lr(n, frac_pct, grid):
+    """tcgen05 logistic step vs PyTorch fp32 (gradient) and vs the CUDA-core kernel (6 SSGD steps)."""
+    from distributed_algorithm_pyspark_b200.config import LogisticConfig
+    from distributed_algorithm_pyspark_b200.models.logistic import ShardedLogisticEngine
+    from distributed_algorithm_pyspark_b200.parallel.dist import init_distributed
+    from distributed_algorithm_pyspark_b200.utils.philox import philox_row_mask_torch
+    dist = init_distributed()
+    dev, D = "cuda", 1024
+    torch.manual_seed(n)
+    X = (torch.randn(n, D, device=dev) * 0.5).to(torch.bfloat16).contiguous()
+    X[:, -1] = 1
+    y = (torch.rand(n, device=dev) < 0.4).float()
+    frac = frac_pct / 100.0
+    cfg = LogisticConfig.for_algo("ssgd" if frac < 1 else "gd", mini_batch_fraction=frac, sample_seed=42, seed=1, eta=0.05 if frac < 1 else 1e-6)
+    eng = ShardedLogisticEngine(X, y, cfg, row_base=500, dist=dist, backend="fused", use_tc=True, grid=grid)
+    assert eng.use_tc
+    w0 = (torch.randn(D, device=dev) * 0.05).contiguous()
+    eng.w.copy_(w0)
+    out = {}
+    for it in (0, 2):
+        eng._launch(_native.FIN_GRAD_ONLY, eng.w, it)
+        torch.cuda.synchronize()
+        keep = philox_row_mask_torch(n, frac, 42, it, 500, device=dev) if frac < 1 else torch.ones(n, dtype=torch.bool, device=dev)
+        Xf = X.float()
+        r = (1.0 / (torch.exp(-(Xf @ w0)) + 1.0) - y) * keep.float()
+        g_ref = r @ Xf
+        out[f"cnt_ok_{it}"] = int(eng.last_count.item()) == int(keep.sum().item())
+        out[f"grad_err_{it}"] = float((eng.g - g_ref).abs().max().item() / (g_ref.abs().max().item() + 1e-12))
+    ref = ShardedLogisticEngine(X, y, cfg, row_base=500, dist=dist, backend="fused", use_tc=False)
+    ref.w.copy_(w0)
+    eng.w.copy_(w0)
+    eng.t = ref.t = 0
+    for _ in range(6):
+        eng.step()
+        ref.step()
+    torch.cuda.synchronize()
+    out["step_err"] = float((eng.w - ref.w).abs().max().item() / (ref.w.abs().max().item() + 1e-12))
+    return out
+
+
 def main():
     kind = sys.argv[1]
     args = list(map(int, sys.argv[2:]))
-    out = {"kmeans": kmeans, "gram": gram}[kind](*args)
+    out = {"kmeans": kmeans, "gram": gram, "lr": lr}[kind](*args)
     print("RESULT " + json.dumps(out))
 
 

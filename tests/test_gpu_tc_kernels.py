@@ -46,3 +46,16 @@ def test_gram_tc_vs_fp64(n, P, splits):
     tol = 2e-5 if n < 100000 else 1e-4        # fp32 accumulation over n rows
     assert r["err1"] < tol and r["err2"] < tol, r
     assert r["sym"] < tol, r
+
+
+@pytest.mark.parametrize("n,frac_pct,grid", [
+    (300, 100, 1),           # 3 tiles (one ragged) in one CTA, every row
+    (5000, 30, 2),           # several tiles per CTA, Bernoulli gather, software pipeline F/B interleave
+    (200000, 10, 0),         # benchmark-like sampling, full grid
+    (1000, 1, 4),            # most CTAs see fewer than one tile of selected rows (some none at all)
+])
+def test_lr_tc_step_vs_fp32_and_cuda_core_kernel(n, frac_pct, grid):
+    r = run_case("lr", n, frac_pct, grid)
+    assert r["cnt_ok_0"] and r["cnt_ok_2"], r
+    assert r["grad_err_0"] < 2e-3 and r["grad_err_2"] < 2e-3, r        # same tolerance as the CUDA-core kernel test
+    assert r["step_err"] < 2e-3, r
