@@ -229,6 +229,19 @@ def main():
     del X, y
     torch.cuda.empty_cache()
     if not args.no_extras:
+        try:    # BASELINE.json config 2 names fp32 as well as bf16: same bytes per GPU, half the rows
+            rows32 = rows // 2
+            X32, y32, _ = synthetic_logistic_device(rows32, args.dim, dev, torch.float32, seed=2000 + dist.rank)
+            args32 = argparse.Namespace(**vars(args))
+            args32.rows_per_gpu = rows32
+            r = bench_logistic(args32, dist, "ssgd", max(5, args.steps // 2), 3, backend, X32, y32)
+            extras["ssgd_fp32_samples_per_s"] = r["samples_per_s"]
+            extras["ssgd_fp32_ms_per_step"] = r["ms_per_step"]
+            extras["ssgd_fp32_hbm_gbs_per_gpu"] = r["samples_per_s"] / dist.world * args.dim * 4 / 1e9
+            del r, X32, y32
+        except Exception as e:
+            extras["ssgd_fp32_error"] = repr(e)[:200]
+        torch.cuda.empty_cache()
         try:
             from benchmarks import extras as ex
             extras.update(ex.run_all(dist, backend))

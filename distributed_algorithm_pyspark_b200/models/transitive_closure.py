@@ -105,12 +105,17 @@ def closure_device(src: torch.Tensor, dst: torch.Tensor, V: int, backend: str = 
     total = int(dist.sum_over_ranks(n_known))
     rounds = 0
     region = None
+    stat = torch.zeros(2, dtype=torch.int64, device=dev)
     while rounds < max_rounds:
         old = total
         fr = frontier[:n_front]
-        bound_local = int(indeg[(fr >> 32)].sum().item()) if n_front else 0      # candidates this rank emits
-        bound_recv = int(dist.max_over_ranks(bound_local)) * (W if W > 1 else 1)  # worst case all to one owner
-        bound_new = bound_local if W == 1 else bound_recv
+        # one host sync + one tiny collective: how many candidates can this round emit (locally / at most per rank)?
+        stat[0] = indeg[(fr >> 32)].sum() if n_front else 0
+        stat[1] = stat[0]
+        if W > 1:
+            torch.distributed.all_reduce(stat[1:], op=torch.distributed.ReduceOp.MAX)
+        bound_local, bound_max = (int(v) for v in stat.tolist())
+        bound_new = bound_local if W == 1 else bound_max * W          # worst case: every rank sends everything to me
         if n_known + bound_new > max_pairs:
             raise MemoryError(f"transitive closure would exceed max_pairs={max_pairs}")
         need = 2 * (n_known + bound_new)
@@ -127,7 +132,7 @@ def closure_device(src: torch.Tensor, dst: torch.Tensor, V: int, backend: str = 
         counters.zero_()
         q_off, q_cap = 0, 0
         if W > 1:
-            q_cap = max(int(dist.max_over_ranks(bound_local)), 1)
+            q_cap = 1 << max(12, int(np.ceil(np.log2(max(bound_max, 1)))))     # power of two: few distinct regions
             region = heap.region(f"tc_queues_{q_cap}", W * (1 + q_cap) * 8, _native.MAX_RANKS)
             q_off = region.payload_off
         _native.check(lib.dapb_tc_expand(heap.comm_ref(), in_ptr.data_ptr(), in_src.data_ptr(), fr.data_ptr(), n_front,
@@ -138,10 +143,16 @@ def closure_device(src: torch.Tensor, dst: torch.Tensor, V: int, backend: str = 
                                                region.next_epoch(), st), "tc_exchange")
             _native.check(lib.dapb_tc_drain(heap.comm_ref(), table.data_ptr(), cap, nxt.data_ptr(), counters.data_ptr(),
                                             q_off, q_cap, st), "tc_drain")
-        n_front = int(counters[0].item())                         # host sync: also orders drain before next expand
+        # second (and last) host sync of the round: local and global number of new pairs; it also orders this
+        # round's drain before the next round's pushes (ref :38-40: the termination test must agree on all ranks)
+        stat[0] = counters[0]
+        stat[1] = counters[0]
+        if W > 1:
+            torch.distributed.all_reduce(stat[1:], op=torch.distributed.ReduceOp.SUM)
+        n_front, new_global = (int(v) for v in stat.tolist())
         frontier = nxt
         n_known += n_front
-        total = int(dist.sum_over_ranks(n_known))                 # ref :38-40 termination must agree on all ranks
+        total += new_global
         rounds += 1
         if total == old:
             break
