@@ -74,6 +74,19 @@ __device__ __forceinline__ uint4 ld_stream_16(const void* p) {
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
   return r;
 }
+// same, with an L2 eviction priority: evict_last for data that will be read once more soon, evict_first for its last use
+__device__ __forceinline__ uint4 ld_stream_16_keep(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.L1::no_allocate.L2::evict_last.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint4 ld_stream_16_last(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.L1::no_allocate.L2::evict_first.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 

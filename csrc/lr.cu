@@ -828,7 +828,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) lr_tc_kernel(DapbLrStepArgs a, 
     const int h = cc >> 3, c8 = cc & 7;
     const char* Xb = reinterpret_cast<const char*>(a.X);
     uint32_t n = 0;
-    auto phase = [&](int t) {
+    auto phase = [&](int t, bool first_pass) {
       const int* lst = list_ptr(t);
       int rows[8];
 #pragma unroll
@@ -839,9 +839,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) lr_tc_kernel(DapbLrStepArgs a, 
         mbar_wait(&slot_empty[slot], ((n / kTcRing) & 1) ^ 1);
         uint4 v[8];
 #pragma unroll
-        for (int it = 0; it < 8; ++it)
-          v[it] = rows[it] >= 0 ? ld_stream_16(Xb + (int64_t)rows[it] * (kTcD * 2) + fb * (kTcFB * 2) + cc * 16)
-                                : make_uint4(0u, 0u, 0u, 0u);
+        for (int it = 0; it < 8; ++it) {
+          const char* src = Xb + (int64_t)rows[it] * (kTcD * 2) + fb * (kTcFB * 2) + cc * 16;
+          // forward pass: keep the line in L2 (evict_last), the backward pass reads it once more and releases it
+          v[it] = rows[it] < 0 ? make_uint4(0u, 0u, 0u, 0u) : (first_pass ? ld_stream_16_keep(src) : ld_stream_16_last(src));
+        }
         uint8_t* dst = smem + slot * kTcSlabBytes + h * (kTcTM * 128);
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
@@ -855,12 +857,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) lr_tc_kernel(DapbLrStepArgs a, 
     };
     mbar_wait(&list_full[0], 0);
     if (list_ptr(0)[0] >= 0) {
-      phase(0);
+      phase(0, true);
       for (int t = 1;; ++t) {
         mbar_wait(&list_full[t % kTcLists], (t / kTcLists) & 1);
         const int nv = list_ptr(t)[0];
-        if (nv >= 0) phase(t);
-        phase(t - 1);                                      // backward pass of the previous tile (L2 hits)
+        if (nv >= 0) phase(t, true);
+        phase(t - 1, false);                               // backward pass of the previous tile (L2 hits)
         __syncwarp();
         if (lane == 0) mbar_arrive(&list_empty[(t - 1) % kTcLists]);
         if (nv < 0) break;

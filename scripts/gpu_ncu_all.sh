@@ -9,7 +9,8 @@ run() {  # name regex skip cmd...
 }
 run kmeans_tc kmeans_tc_kernel 0 python tests/_tc_worker.py kmeans 8000000 128 1024 0
 run gram_tc gram_tc_kernel 0 python tests/_tc_worker.py gram 2000000 512 0
-run lr_step lr_step_kernel 2 python bench.py --steps 3 --warmup 1 --no-extras --no-e2e --rows-per-gpu 4194304
+run lr_step lr_step_kernel 2 python bench.py --steps 3 --warmup 1 --no-extras --no-e2e --rows-per-gpu 8388608
+run lr_tc lr_tc_kernel 2 python bench.py --steps 3 --warmup 1 --no-extras --no-e2e --rows-per-gpu 8388608 --lr-kernel tc
 run pagerank pagerank_step_kernel 3 python -m benchmarks.extras --only pagerank --pagerank-scale 22
 run mc_pi mc_pi_kernel 0 python -m benchmarks.extras --only mc
 ls -la gpurun_out/*.ncu-rep
