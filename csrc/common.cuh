@@ -74,19 +74,16 @@ __device__ __forceinline__ uint4 ld_stream_16(const void* p) {
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
   return r;
 }
-// same, with an L2 eviction priority: evict_last for data that will be read once more soon, evict_first for its last use
-__device__ __forceinline__ uint4 ld_stream_16_keep(const void* p) {
+// same, with an L2 cache-policy operand (createpolicy encodings, as used for TMA cache hints): evict_last for data
+// that will be read once more soon, evict_first for its last use
+__device__ __forceinline__ uint4 ld_stream_16_hint(const void* p, uint64_t policy) {
   uint4 r;
-  asm volatile("ld.global.L1::no_allocate.L2::evict_last.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(policy));
   return r;
 }
-__device__ __forceinline__ uint4 ld_stream_16_last(const void* p) {
-  uint4 r;
-  asm volatile("ld.global.L1::no_allocate.L2::evict_first.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-  return r;
-}
+__device__ __forceinline__ uint4 ld_stream_16_keep(const void* p) { return ld_stream_16_hint(p, 0x14F0000000000000ull); }
+__device__ __forceinline__ uint4 ld_stream_16_last(const void* p) { return ld_stream_16_hint(p, 0x12F0000000000000ull); }
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 
