@@ -152,14 +152,18 @@ def bench_tc(dist, backend, V=2_000_000, E=1_000_000):
     g = torch.Generator(device=dev).manual_seed(3)
     src = torch.randint(0, V, (E,), device=dev, generator=g)
     dst = torch.randint(0, V, (E,), device=dev, generator=g)
-    closure_device(src[:1000], dst[:1000], V, "fused" if backend == "fused" else "torch", dist)   # warm-up
-    torch.cuda.synchronize()
-    dist.barrier()
-    t0 = time.perf_counter()
-    total, rounds, _ = closure_device(src, dst, V, "fused" if backend == "fused" else "torch", dist)
-    torch.cuda.synchronize()
-    ms = dist.max_over_ranks((time.perf_counter() - t0) * 1e3)
-    return {"tc_pairs": total, "tc_rounds": rounds, "tc_ms": ms, "tc_pairs_per_s": total / (ms / 1e3)}
+    be = "fused" if backend == "fused" else "torch"
+    closure_device(src, dst, V, be, dist)          # warm-up at full size (allocator pools, heap regions, module load)
+    best = None
+    for _ in range(3):
+        torch.cuda.synchronize()
+        dist.barrier()
+        t0 = time.perf_counter()
+        total, rounds, _ = closure_device(src, dst, V, be, dist)   # includes de-duplication and the CSR build
+        torch.cuda.synchronize()
+        ms = dist.max_over_ranks((time.perf_counter() - t0) * 1e3)
+        best = ms if best is None else min(best, ms)
+    return {"tc_pairs": total, "tc_rounds": rounds, "tc_ms": best, "tc_pairs_per_s": total / (best / 1e3)}
 
 
 ALL = {"kmeans": bench_kmeans, "pagerank": bench_pagerank, "gram": bench_gram, "mc": bench_monte_carlo, "tc": bench_tc}

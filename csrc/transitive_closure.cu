@@ -7,9 +7,11 @@
 // unchanged).  The reference re-joins ALL paths every round; joining only the pairs discovered in
 // the previous round (semi-naive evaluation) yields the same set after the same number of rounds
 // because every older pair's extensions were already produced.
+#include <cooperative_groups.h>
 #include "comm.cuh"
 
 using namespace dapb;
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -106,6 +108,162 @@ __global__ void tc_seed_kernel(const unsigned long long* keys, int64_t n, unsign
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Persistent closure kernel: ALL rounds in one cooperative launch.  Per round
+//   expand   every CTA joins its part of the frontier with the in-edge CSR and pushes each candidate
+//            (x, z) into the hash owner's queue in peer memory (parity-double-buffered),
+//   exchange CTA 0 all-gathers one 16-word message per rank {W queue tails, |frontier|, |known|,
+//            table capacity, frontier capacity}: this single exchange is the queue-publish barrier,
+//            the termination test (ref :38-40, identical on every rank) and the capacity check,
+//   drain    every CTA inserts the candidates queued for this rank; new pairs form the next frontier.
+// Three grid syncs and one cross-rank exchange per round, no host involvement.  If any queue,
+// table or frontier would overflow, every rank sees it in the same message matrix and leaves
+// BEFORE draining (nothing was inserted, so the round can be repeated after the host has grown
+// the buffers).
+// state words (u64): see TcS below.
+// ---------------------------------------------------------------------------------------------
+enum TcS { S_CNT0 = 0, S_CNT1 = 1, S_CUR = 2, S_KNOWN = 3, S_TOTAL = 4, S_ROUNDS = 5, S_STATUS = 6, S_EPOCH = 7,
+           S_NEED_Q = 8, S_NEED_TABLE = 9, S_NEED_FRONT = 10, S_TAILS = 16 /* .. 16 + DAPB_MAX_RANKS */ };
+constexpr int kTcMsg = 16;                 // u64 words per rank message
+
+struct TcRunArgs {
+  const int64_t* in_ptr;
+  const int32_t* in_src;
+  unsigned long long* table;
+  uint64_t mask;
+  unsigned long long* front[2];
+  uint64_t front_cap;
+  unsigned long long* state;
+  uint64_t q_off;              // queues: [parity 2][src rank W][q_cap] u64 in every rank's heap
+  uint64_t q_cap;
+  uint64_t msg_off;            // messages: [parity 2][rank W][kTcMsg] u64 in every rank's heap
+  uint32_t flag_base;          // W flags
+  uint64_t max_rounds;
+};
+
+// warp-aggregated slot allocation: lanes of the calling (possibly diverged) group that target the same counter
+// take consecutive slots with one atomic
+__device__ __forceinline__ unsigned long long agg_alloc(unsigned long long* counters, int which) {
+  const unsigned act = __activemask();
+  const unsigned peers = __match_any_sync(act, which);
+  const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
+  unsigned long long base = 0;
+  if (lane == leader) base = atomicAdd(counters + which, (unsigned long long)__popc(peers));
+  base = __shfl_sync(peers, base, leader);
+  return base + __popc(peers & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(256) tc_closure_kernel(TcRunArgs a, DapbComm c) {
+  cg::grid_group grid = cg::this_grid();
+  volatile unsigned long long* st = a.state;
+  __shared__ unsigned long long s_mat[DAPB_MAX_RANKS * kTcMsg];
+  const int W = c.world, me = c.rank;
+  uint64_t cur = st[S_CUR], epoch = st[S_EPOCH], rounds = st[S_ROUNDS];
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+
+  for (;;) {
+    const uint64_t par = epoch & 1;            // parity of THIS round's exchange = queue / message buffer
+    // ---------------- expand
+    {
+      const uint64_t n_front = st[S_CNT0 + cur];
+      const unsigned long long* fr = a.front[cur];
+      for (int64_t i = tid; i < (int64_t)n_front; i += nthreads) {
+        const uint64_t yz = fr[i];
+        const uint32_t y = (uint32_t)(yz >> 32), z = (uint32_t)yz;
+        const int64_t e0 = a.in_ptr[y], e1 = a.in_ptr[y + 1];
+        for (int64_t e = e0; e < e1; ++e) {
+          const uint64_t key = ((uint64_t)(uint32_t)a.in_src[e] << 32) | z;          // new path (x, z)
+          const int owner = W == 1 ? 0 : (int)hash_owner(key, (uint32_t)W);
+          const unsigned long long pos = agg_alloc(a.state + S_TAILS, owner);
+          if (pos < a.q_cap)
+            reinterpret_cast<unsigned long long*>(comm_payload(c, owner, a.q_off))[(par * W + me) * a.q_cap + pos] = key;
+        }
+      }
+    }
+    grid.sync();
+    // ---------------- exchange (CTA 0)
+    if (blockIdx.x == 0) {
+      const uint64_t ep = epoch + 1;
+      if (threadIdx.x < kTcMsg) {
+        unsigned long long v = 0;
+        const int t = threadIdx.x;
+        if (t < W) v = st[S_TAILS + t];
+        else if (t == 8) v = st[S_CNT0 + cur];
+        else if (t == 9) v = st[S_KNOWN];
+        else if (t == 10) v = a.mask + 1;
+        else if (t == 11) v = a.front_cap;
+        for (int r = 0; r < W; ++r)
+          reinterpret_cast<unsigned long long*>(comm_payload(c, r, a.msg_off))[((ep & 1) * W + me) * kTcMsg + t] = v;
+      }
+      if (W > 1) {
+        block_signal_all(c, me, a.flag_base, ep);
+        block_wait_all(c, me, a.flag_base, ep);
+      } else {
+        __syncthreads();
+      }
+      if (threadIdx.x < W * kTcMsg)
+        s_mat[threadIdx.x] = __ldcg(reinterpret_cast<const unsigned long long*>(comm_payload(c, me, a.msg_off)) +
+                                    (ep & 1) * W * kTcMsg + threadIdx.x);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        uint64_t new_global = 0, total = 0, need_q = 0, need_table = 0, need_front = 0;
+        bool grow = false;
+        for (int r = 0; r < W; ++r) {
+          new_global += s_mat[r * kTcMsg + 8];
+          total += s_mat[r * kTcMsg + 9];
+          uint64_t incoming = 0;
+          for (int s = 0; s < W; ++s) {
+            const uint64_t t = s_mat[s * kTcMsg + r];
+            incoming += t;
+            need_q = t > need_q ? t : need_q;
+          }
+          const uint64_t want_table = 2 * (s_mat[r * kTcMsg + 9] + incoming);
+          if (want_table > s_mat[r * kTcMsg + 10] || incoming > s_mat[r * kTcMsg + 11]) grow = true;
+          if (r == me) { need_table = want_table; need_front = incoming; }
+        }
+        if (need_q > a.q_cap) grow = true;
+        st[S_TOTAL] = total;
+        st[S_NEED_Q] = need_q; st[S_NEED_TABLE] = need_table; st[S_NEED_FRONT] = need_front;
+        uint64_t status = DAPB_TC_RUNNING;
+        if ((rounds > 0 && new_global == 0) || rounds >= a.max_rounds) status = DAPB_TC_DONE;
+        else if (grow) status = DAPB_TC_GROW;
+        st[S_STATUS] = status;
+        st[S_EPOCH] = ep;
+        st[S_CNT0 + (cur ^ 1)] = 0;             // tail of the frontier this round's drain will build
+      }
+      if (threadIdx.x < DAPB_MAX_RANKS) st[S_TAILS + threadIdx.x] = 0;
+      __threadfence();
+    }
+    grid.sync();
+    ++epoch;
+    if (st[S_STATUS] != DAPB_TC_RUNNING) return;   // DONE, or GROW (same frontier is expanded again after growth)
+    // ---------------- drain
+    {
+      const unsigned long long* msg = reinterpret_cast<const unsigned long long*>(comm_payload(c, me, a.msg_off)) +
+                                      (epoch & 1) * W * kTcMsg;
+      unsigned long long* nxt = a.front[cur ^ 1];
+      for (int s = 0; s < W; ++s) {
+        const uint64_t n = __ldcg(msg + s * kTcMsg + me);
+        const unsigned long long* q = reinterpret_cast<const unsigned long long*>(comm_payload(c, me, a.q_off)) +
+                                      (par * W + s) * a.q_cap;
+        for (int64_t i = tid; i < (int64_t)n; i += nthreads) {
+          const uint64_t key = __ldcg(q + i);
+          if (hs_insert(a.table, a.mask, key)) nxt[agg_alloc(a.state + S_CNT0, (int)(cur ^ 1))] = key;
+        }
+      }
+    }
+    grid.sync();
+    cur ^= 1;
+    ++rounds;
+    if (tid == 0) {
+      st[S_KNOWN] = st[S_KNOWN] + st[S_CNT0 + cur];
+      st[S_CUR] = cur;
+      st[S_ROUNDS] = rounds;
+    }
+  }
+}
+
 int grid_for(int64_t n) {
   int64_t b = (n + 255) / 256;
   const int64_t cap = (int64_t)dapb::sm_count() * 8;
@@ -165,5 +323,37 @@ extern "C" int dapb_tc_drain(const DapbComm* comm, unsigned long long* table, ui
   a.q_off = q_off; a.q_cap = q_cap;
   tc_drain_kernel<<<dapb::sm_count() * 4, 256, 0, (cudaStream_t)stream>>>(a, *comm);
   DAPB_LAUNCH_CHECK();
+  return 0;
+}
+
+// All rounds of the closure in one cooperative launch (see tc_closure_kernel).  `state` holds DAPB_TC_STATE_WORDS
+// u64 words: the caller seeds the first frontier into frontier0 with dapb_tc_seed(out_count = state + 0), sets
+// state[3] (= known) to the same count and state[7] to the epoch of the message region, and reads back
+// state[4] = global pair count, state[5] = rounds, state[6] = DAPB_TC_DONE / DAPB_TC_GROW (then state[8..10] = needed
+// queue / table / frontier capacities of this rank) and state[7] = epoch to store back into the region.
+extern "C" int dapb_tc_closure(const DapbComm* comm, const int64_t* in_ptr, const int32_t* in_src,
+                               unsigned long long* table, uint64_t capacity, unsigned long long* frontier0,
+                               unsigned long long* frontier1, uint64_t front_cap, unsigned long long* state,
+                               uint64_t q_off, uint64_t q_cap, uint64_t msg_off, uint32_t flag_base,
+                               uint64_t max_rounds, void* stream) {
+  DAPB_REQUIRE(comm && comm->world >= 1 && comm->world <= DAPB_MAX_RANKS, "tc_closure: bad comm");
+  DAPB_REQUIRE(capacity >= 2 && (capacity & (capacity - 1)) == 0, "tc_closure: capacity must be a power of two");
+  const uint64_t W = (uint64_t)comm->world;
+  DAPB_REQUIRE(DAPB_FLAG_BYTES + q_off + 2 * W * q_cap * 8 <= comm->heap_bytes &&
+               DAPB_FLAG_BYTES + msg_off + 2 * W * kTcMsg * 8 <= comm->heap_bytes,
+               "tc_closure: heap too small for queues / messages");
+  DAPB_REQUIRE((flag_base + W) * 8ull <= DAPB_FLAG_BYTES, "tc_closure: flag range");
+  static int per_sm = 0;
+  if (!per_sm) {
+    DAPB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tc_closure_kernel, 256, 0));
+    if (per_sm > 4) per_sm = 4;
+    DAPB_REQUIRE(per_sm >= 1, "tc_closure: kernel does not fit on an SM");
+  }
+  TcRunArgs a{in_ptr, in_src, table, capacity - 1, {frontier0, frontier1}, front_cap, state,
+              q_off, q_cap, msg_off, flag_base, max_rounds};
+  DapbComm c = *comm;
+  void* kargs[] = {&a, &c};
+  DAPB_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)tc_closure_kernel, dim3(dapb::sm_count() * per_sm), dim3(256),
+                                              kargs, 0, (cudaStream_t)stream));
   return 0;
 }

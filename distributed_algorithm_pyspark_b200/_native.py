@@ -14,6 +14,7 @@ from . import build as _build
 
 MAX_RANKS = 8
 FLAG_BYTES = 65536
+TC_STATE_WORDS, TC_RUNNING, TC_DONE, TC_GROW = 32, 0, 1, 2
 
 _lib: Optional[C.CDLL] = None
 _load_error: Optional[str] = None
@@ -102,6 +103,7 @@ def _declare(lib: C.CDLL):
         "dapb_tc_expand": (C.c_int, [P(DapbComm), vp, vp, vp, i64, vp, u64, vp, vp, u64, u64, vp]),
         "dapb_tc_exchange": (C.c_int, [P(DapbComm), vp, u64, u64, u32, u64, vp]),
         "dapb_tc_drain": (C.c_int, [P(DapbComm), vp, u64, vp, vp, u64, u64, vp]),
+        "dapb_tc_closure": (C.c_int, [P(DapbComm), vp, vp, vp, u64, vp, vp, u64, vp, u64, u64, u64, u32, u64, vp]),
         "dapb_gram": (C.c_int, [P(DapbComm), vp, vp, i64, i32, i32, i64, i64, i32, vp, i32, vp, vp, u64, u32, u64, i32, vp]),
         "dapb_gram_tc": (C.c_int, [P(DapbComm), vp, i64, i32, vp, vp, i32, u64, u32, u64, i32, vp]),
         "dapb_gram_tc_payload_bytes": (u64, [i32, i32]),

@@ -12,6 +12,7 @@ Backends: ``oracle`` (Python sets), ``torch`` (sort/unique based, ``all_to_all``
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import Iterable, Optional, Tuple
 
@@ -47,11 +48,14 @@ def _in_csr(src: torch.Tensor, dst: torch.Tensor, V: int):
 
 def closure_device(src: torch.Tensor, dst: torch.Tensor, V: int, backend: str = "fused",
                    dist: Optional[Dist] = None, max_rounds: int = 1 << 20, keep_pairs: bool = False,
-                   heap=None, max_pairs: int = 1 << 28) -> Tuple[int, int, Optional[torch.Tensor]]:
+                   heap=None, max_pairs: int = 1 << 28, persistent: Optional[bool] = None
+                   ) -> Tuple[int, int, Optional[torch.Tensor]]:
     """Closure of a graph with vertex ids 0..V-1 (the FULL edge list on every rank, int64 on device).
     Returns (global pair count, rounds, local keys or None)."""
     dist = dist or current()
     dev = src.device
+    if persistent is None:
+        persistent = os.environ.get("DAPB_TC_ROUNDS") is None
     ekeys = torch.unique(_pack(src, dst))
     src_u, dst_u = (ekeys >> 32), (ekeys & 0xFFFFFFFF)
     in_ptr, in_src, indeg = _in_csr(src_u, dst_u, V)
@@ -97,9 +101,12 @@ def closure_device(src: torch.Tensor, dst: torch.Tensor, V: int, backend: str = 
     cap = 1 << max(10, int(np.ceil(np.log2(max(4 * ekeys.numel() // max(W, 1), 1024)))))
     table = torch.full((cap,), -1, dtype=u64, device=dev)
     counters = torch.zeros(1 + _native.MAX_RANKS, dtype=u64, device=dev)
-    frontier = torch.empty(max(ekeys.numel(), 1), dtype=u64, device=dev)
+    frontier = torch.empty(_pow2(ekeys.numel()) if persistent else max(ekeys.numel(), 1), dtype=u64, device=dev)
     _native.check(lib.dapb_tc_seed(ekeys.data_ptr(), ekeys.numel(), table.data_ptr(), cap, frontier.data_ptr(),
                                    counters.data_ptr(), W, me, st), "tc_seed")
+    if persistent:
+        return _closure_persistent(lib, heap, dist, in_ptr, in_src, ekeys, table, cap, frontier, counters, max_rounds,
+                                   max_pairs, keep_pairs)
     n_front = int(counters[0].item())
     n_known = n_front
     total = int(dist.sum_over_ranks(n_known))
@@ -158,6 +165,64 @@ def closure_device(src: torch.Tensor, dst: torch.Tensor, V: int, backend: str = 
             break
     keys = table[table != -1] if keep_pairs else None
     return total, rounds, keys
+
+
+def _pow2(n: int, lo: int = 4096) -> int:
+    return 1 << max(int(np.ceil(np.log2(max(n, 1)))), int(np.log2(lo)))
+
+
+def _closure_persistent(lib, heap, dist, in_ptr, in_src, ekeys, table, cap, frontier0, counters, max_rounds,
+                        max_pairs, keep_pairs):
+    """All rounds in one cooperative launch (``dapb_tc_closure``): the kernel returns only when the closure is complete
+    or a buffer must grow.  Buffer growth is decided from the same in-kernel message matrix on every rank, so the
+    host loop needs no collective of its own."""
+    dev, W = in_ptr.device, dist.world
+    st = _native.stream_ptr()
+    u64 = torch.int64
+    n_e = ekeys.numel()
+    state = torch.zeros(_native.TC_STATE_WORDS, dtype=u64, device=dev)
+    state[0] = counters[0]
+    state[3] = counters[0]
+    front_cap = frontier0.numel()                       # >= number of seeds on any rank
+    fronts = [frontier0, torch.empty_like(frontier0)]
+    q_cap = _pow2(n_e // W)
+    msg = heap.region("tc_msg", 2 * _native.MAX_RANKS * 16 * 8, _native.MAX_RANKS)
+    torch.cuda.synchronize()
+    dist.barrier()                       # nobody may still be using the queues / messages of a previous closure
+    while True:
+        q = heap.region(f"tc_pq_{q_cap}", 2 * W * q_cap * 8, 0)
+        state[7] = msg.epoch
+        _native.check(lib.dapb_tc_closure(heap.comm_ref(), in_ptr.data_ptr(), in_src.data_ptr(), table.data_ptr(), cap,
+                                          fronts[0].data_ptr(), fronts[1].data_ptr(), front_cap, state.data_ptr(),
+                                          q.payload_off, q_cap, msg.payload_off, msg.flag_base, max_rounds, st),
+                      "tc_closure")
+        h = state.tolist()
+        msg.epoch = h[7]
+        if h[6] == _native.TC_DONE:
+            break
+        assert h[6] == _native.TC_GROW, f"tc_closure: unexpected status {h[6]}"
+        need_q, need_table, need_front = h[8], h[9], h[10]
+        if need_table // 2 > max_pairs:
+            raise MemoryError(f"transitive closure would exceed max_pairs={max_pairs}")
+        if need_q > q_cap:
+            q_cap = _pow2(2 * need_q)
+        if need_front > front_cap:
+            new_cap = _pow2(2 * need_front)
+            grown = [torch.empty(new_cap, dtype=u64, device=dev) for _ in range(2)]
+            cur = h[2]
+            grown[cur][:h[cur]] = fronts[cur][:h[cur]]
+            fronts, front_cap = grown, new_cap
+        if need_table > cap:
+            new_cap = _pow2(2 * need_table)
+            old_keys = table[table != -1]
+            table = torch.full((new_cap,), -1, dtype=u64, device=dev)
+            scratch = torch.empty(max(old_keys.numel(), 1), dtype=u64, device=dev)
+            cnt = torch.zeros(1, dtype=u64, device=dev)
+            _native.check(lib.dapb_tc_seed(old_keys.data_ptr(), old_keys.numel(), table.data_ptr(), new_cap,
+                                           scratch.data_ptr(), cnt.data_ptr(), 1, 0, st), "tc_seed(rehash)")
+            cap = new_cap
+    keys = table[table != -1] if keep_pairs else None
+    return int(h[4]), int(h[5]), keys
 
 
 def run_transitive_closure(edges: Iterable[Tuple[int, int]], cfg: Optional[TransitiveClosureConfig] = None,

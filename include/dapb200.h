@@ -216,6 +216,19 @@ DAPB_API int dapb_tc_drain(const DapbComm* comm, unsigned long long* table, uint
                            unsigned long long* next_frontier, unsigned long long* counters, uint64_t q_off,
                            uint64_t q_cap, void* stream);
 
+/* Persistent variant: every round of the closure in ONE cooperative launch (expand -> in-kernel all-gather of the
+ * queue tails / termination test / capacity check -> drain).  See csrc/transitive_closure.cu for the state words. */
+#define DAPB_TC_STATE_WORDS 32
+#define DAPB_TC_RUNNING 0
+#define DAPB_TC_DONE 1
+#define DAPB_TC_GROW 2
+DAPB_API int dapb_tc_closure(const DapbComm* comm, const int64_t* in_ptr, const int32_t* in_src,
+                             unsigned long long* table, uint64_t capacity, unsigned long long* frontier0,
+                             unsigned long long* frontier1, uint64_t front_cap, unsigned long long* state,
+                             uint64_t q_off, uint64_t q_cap, uint64_t msg_off, uint32_t flag_base,
+                             uint64_t max_rounds, void* stream);
+
+
 /* ------------------------------------------------------------------ F5 Gram / ALS ----------
  * ref: matrix_computation/matrix_decomposition.py:19-33,51-67.  dtype: 0 fp32, 1 bf16, 2 fp64. */
 DAPB_API int dapb_gram(const DapbComm* comm, const void* X, const void* Y, int64_t n, int32_t P, int32_t Q,

@@ -269,6 +269,23 @@ def test_transitive_closure_fused_vs_oracle(dist):
     assert sorted(map(tuple, got.pairs.tolist())) == sorted(pairs)
 
 
+@pytest.mark.parametrize("persistent", [True, False])
+def test_transitive_closure_growth_paths(dist, persistent):
+    """Supercritical graph: the closure is ~100x the edge count, so tables / frontiers / queues must grow mid-run
+    (persistent kernel: status GROW -> host grows -> relaunch of the same round)."""
+    from distributed_algorithm_pyspark_b200.models.transitive_closure import closure_device
+    rs = np.random.RandomState(11)
+    V, E = 700, 1500
+    src, dst = rs.randint(0, V, E), rs.randint(0, V, E)
+    n, rounds, pairs = transitive_closure_oracle(list(zip(src.tolist(), dst.tolist())))
+    assert n > 50 * E
+    tot, r, keys = closure_device(torch.tensor(src, device=DEV), torch.tensor(dst, device=DEV), V, "fused", dist,
+                                  keep_pairs=True, persistent=persistent)
+    assert (tot, r) == (n, rounds)
+    k = keys.cpu().numpy()
+    assert sorted(zip((k >> 32).tolist(), (k & 0xFFFFFFFF).tolist())) == sorted(pairs)
+
+
 # ------------------------------------------------------------------------------------------ F5
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2), (torch.float64, 1e-11)])
 def test_gram_vs_torch(dist, dtype, tol):
