@@ -12,6 +12,7 @@ fuses reduce-scatter, mean update and centroid all-gather over NVLink peer memor
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import numpy as np
@@ -23,6 +24,7 @@ from ..oracle import spark_semantics as sp
 from ..oracle.algorithms import KMeansResult, kmeans_oracle
 from ..parallel.dist import Dist, current
 from ..parallel.partition import RowSharding
+from ..utils import checkpoint as ck
 from ..utils.trace import span
 
 _DT = {torch.float32: 0, torch.bfloat16: 1, torch.float64: 2}
@@ -34,8 +36,10 @@ def initial_center_indices(n_points: int, cfg: KMeansConfig):
 
 
 def run_kmeans(points: np.ndarray, cfg: KMeansConfig, backend: str = "auto", dist: Optional[Dist] = None,
-               init_centers: Optional[np.ndarray] = None) -> KMeansResult:
-    """Cluster a host array the way the reference script does (small / parity problems)."""
+               init_centers: Optional[np.ndarray] = None, checkpoint: Optional[str] = None,
+               checkpoint_every: int = 0, resume: bool = False) -> KMeansResult:
+    """Cluster a host array the way the reference script does (small / parity problems).
+    ``checkpoint`` / ``checkpoint_every`` / ``resume``: centres + iteration counter (utils/checkpoint.py)."""
     if backend == "auto":
         backend = "fused" if _native.available() else "torch"
     if backend == "oracle":
@@ -50,10 +54,19 @@ def run_kmeans(points: np.ndarray, cfg: KMeansConfig, backend: str = "auto", dis
     X = torch.as_tensor(np.ascontiguousarray(pts[r0:r1]), dtype=torch.float64, device=dist.device)
     eng = ShardedKMeans(X, cfg.k, torch.as_tensor(c0, dtype=torch.float64, device=dist.device), dist=dist,
                         backend="fused" if backend == "fused" else "nccl")
-    history = []
-    for _ in range(cfg.n_iterations):
+    history, t0 = [], 0
+    meta = dict(kind="kmeans", k=int(cfg.k), dim=int(pts.shape[1]), n_points=int(n))
+    if checkpoint and resume and os.path.exists(checkpoint):
+        st, m = ck.load_checkpoint(checkpoint)
+        ck.check_meta(m, **meta)
+        t0, history = int(m["iteration"]), list(st["history"])
+        eng.centers.copy_(torch.as_tensor(st["centers"], dtype=eng.centers.dtype))
+    for t in range(t0, cfg.n_iterations):
         eng.step()
         history.append(eng.centers.cpu().numpy().copy())
+        if checkpoint and checkpoint_every > 0 and ((t + 1) % checkpoint_every == 0 or t + 1 == cfg.n_iterations) \
+                and dist.is_main:
+            ck.save_checkpoint(checkpoint, dict(centers=history[-1], history=np.stack(history)), dict(meta, iteration=t + 1))
     assign_local = eng.assign()                                    # final centres (ref k-means.py:76, A.7)
     parts = dist.all_gather_object(assign_local.cpu().numpy())
     return KMeansResult(centers=eng.centers.cpu().numpy(), assignment=np.concatenate(parts).astype(np.int64),
@@ -89,6 +102,14 @@ class ShardedKMeans:
                 use_tc = kmeans_tc.supported(self.X, self.k)
             if use_tc:
                 self.tc = kmeans_tc.KMeansTC(self.X, self.k)
+
+    def state_dict(self) -> dict:
+        """Everything a resumed run needs (utils/checkpoint.py); replicated, so rank 0's copy is enough."""
+        return {"centers": self.centers.detach().cpu().numpy(), "iteration": np.int64(self.iteration)}
+
+    def load_state_dict(self, st: dict):
+        self.centers.copy_(torch.as_tensor(np.asarray(st["centers"]), dtype=self.acc_dtype))
+        self.iteration = int(st["iteration"])
 
     def step(self):
         """One Lloyd iteration (ref k-means.py:55-71)."""

@@ -53,11 +53,18 @@ def _resolve_backend(backend: str) -> str:
 
 def run_logistic(data: LogisticData, cfg: LogisticConfig, init: Optional[LogisticInit] = None,
                  backend: str = "auto", dist: Optional[Dist] = None,
-                 masks: Optional[np.ndarray] = None, record_w: bool = False) -> LogisticResult:
-    """Train on ``data`` exactly as the reference script for ``cfg.algo`` does."""
+                 masks: Optional[np.ndarray] = None, record_w: bool = False,
+                 checkpoint: Optional[str] = None, checkpoint_every: int = 0, resume: bool = False) -> LogisticResult:
+    """Train on ``data`` exactly as the reference script for ``cfg.algo`` does.
+
+    ``checkpoint`` + ``checkpoint_every=k`` write the optimiser state (w, replicas, BMUF momentum, accuracy history)
+    every k iterations; ``resume=True`` continues from that file (utils/checkpoint.py).  The resumed trajectory is
+    identical to the uninterrupted one because iteration t's mini-batch depends only on (seed, t)."""
     backend = _resolve_backend(backend)
     if init is None:
         init = LogisticInit.draw(cfg.algo, data.dim, cfg.n_slices, cfg.seed)
+    if checkpoint and (checkpoint_every > 0 or resume):
+        return _run_segmented(data, cfg, init, backend, dist, masks, checkpoint, checkpoint_every, resume)
     if backend == "oracle":
         return logistic_oracle(data.matrix, data.X_test_aug, data.y_test, cfg, init,
                                masks=None if masks is None else masks.astype(bool))
@@ -70,6 +77,46 @@ def run_logistic(data: LogisticData, cfg: LogisticConfig, init: Optional[Logisti
     if backend == "fused":
         return _run_fused_parity(data, cfg, init, dist, sh, masks, record_w)
     raise ValueError(f"unknown backend {backend!r}")
+
+
+def _run_segmented(data, cfg, init, backend, dist, masks, path, every, resume) -> LogisticResult:
+    """Run ``cfg.n_iterations`` iterations in segments of ``every``, saving a checkpoint after each segment."""
+    import dataclasses
+    from ..utils import checkpoint as ck
+    T = cfg.n_iterations
+    if backend != "oracle":
+        dist = dist or current()
+    is_main = dist is None or dist.is_main
+    if masks is None:
+        sizes = RowSharding.spark(data.matrix.shape[0], cfg.n_slices, 1 if dist is None else dist.world).sizes()
+        masks = sample_masks(cfg, sizes)
+    t0, accs, bsz = 0, [], []
+    meta = dict(kind="logistic", algo=cfg.algo, dim=int(data.dim), n_slices=int(cfg.n_slices), sampler=cfg.sampler,
+                sample_seed=int(cfg.sample_seed))
+    if resume:
+        import os
+        if os.path.exists(path):
+            st, m = ck.load_checkpoint(path)
+            ck.check_meta(m, **meta)
+            t0 = int(m["iteration"])
+            init = LogisticInit(w=st["w"], ws=st.get("ws"), delta_w=st.get("delta_w"))
+            accs, bsz = st["accs"].tolist(), st["batch_sizes"].tolist()
+        elif is_main:
+            print(f"resume: no checkpoint at {path}, starting from iteration 0")
+    every = every if every > 0 else max(T - t0, 1)
+    res = LogisticResult(w=init.w, accs=accs, batch_sizes=bsz, ws=init.ws, delta_w=init.delta_w)
+    while t0 < T:
+        t1 = min(T, t0 + every)
+        seg_cfg = dataclasses.replace(cfg, n_iterations=t1 - t0)
+        seg = run_logistic(data, seg_cfg, init, backend, dist, None if masks is None else masks[t0:t1])
+        accs, bsz = accs + list(seg.accs), bsz + list(seg.batch_sizes)
+        init = LogisticInit(w=seg.w, ws=seg.ws if seg.ws is not None else init.ws, delta_w=seg.delta_w)
+        res = LogisticResult(w=seg.w, accs=accs, batch_sizes=bsz, ws=seg.ws, delta_w=seg.delta_w)
+        t0 = t1
+        if is_main:
+            ck.save_checkpoint(path, dict(w=res.w, ws=init.ws, delta_w=init.delta_w, accs=np.asarray(accs, dtype=np.float64),
+                                          batch_sizes=np.asarray(bsz, dtype=np.int64)), dict(meta, iteration=t0))
+    return res
 
 
 # ------------------------------------------------------------------------------------------------ torch baseline
@@ -308,6 +355,18 @@ class ShardedLogisticEngine:
             a.epoch = self.region.next_epoch()
         fn = self.lib.dapb_lr_step_tc if self.use_tc else self.lib.dapb_lr_step
         _native.check(fn(C.byref(a), self.heap.comm_ref(), _native.stream_ptr(stream)), "lr_step")
+
+    def state_dict(self) -> dict:
+        """Optimiser state: global ``w`` and BMUF momentum are replicated; ``w_local`` (the EASGD replica) is
+        rank-local and belongs in ``checkpoint.rank_path(path, rank)``.  The mini-batch of iteration t is a pure
+        function of (seed, t, row), so ``t`` is all the sampler state there is."""
+        return {"w": self.w.detach().cpu().numpy(), "w_local": self.w_local.detach().cpu().numpy(),
+                "delta_w": self.delta_w.detach().cpu().numpy(), "t": np.int64(self.t)}
+
+    def load_state_dict(self, st: dict):
+        for name in ("w", "w_local", "delta_w"):
+            getattr(self, name).copy_(torch.as_tensor(np.asarray(st[name]), dtype=torch.float32))
+        self.t = int(st["t"])
 
     def step(self, stream=None):
         """One outer iteration / communication round of ``cfg.algo`` (ref loop bodies cited above)."""

@@ -18,6 +18,7 @@ Backends: ``oracle`` (NumPy, per-row solves as the reference), ``torch`` (matmul
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import List, Optional, Tuple
 
@@ -29,6 +30,7 @@ from ..config import ALSConfig
 from ..oracle.algorithms import als_draw, als_oracle
 from ..parallel.dist import Dist, current
 from ..parallel.partition import RowSharding
+from ..utils import checkpoint as ck
 
 _DT = {torch.float32: 0, torch.bfloat16: 1, torch.float64: 2}
 
@@ -75,8 +77,11 @@ class GramOp:
 
 def run_als(cfg: ALSConfig, R: Optional[np.ndarray] = None, U0: Optional[np.ndarray] = None,
             V0: Optional[np.ndarray] = None, backend: str = "auto", dist: Optional[Dist] = None,
-            dtype=torch.float64, callback=None) -> ALSResult:
-    """ALS exactly as the reference drives it; ``R``/``U0``/``V0`` default to the reference's draws (:42-44)."""
+            dtype=torch.float64, callback=None, checkpoint: Optional[str] = None, checkpoint_every: int = 0,
+            resume: bool = False) -> ALSResult:
+    """ALS exactly as the reference drives it; ``R``/``U0``/``V0`` default to the reference's draws (:42-44).
+    ``checkpoint``: V (replicated), the rmse history and the iteration counter; U is recomputed from V each
+    iteration (:52-56); it is stored only so that a finished run can be reloaded."""
     if backend == "auto":
         backend = "fused" if _native.available() else "torch"
     if R is None:
@@ -106,7 +111,15 @@ def run_als(cfg: ALSConfig, R: Optional[np.ndarray] = None, U0: Optional[np.ndar
         g_ru = GramOp(n, k, dtype, dev, dist, tag="ru")
         B = torch.empty(r1 - r0, k, dtype=dtype, device=dev)
         sq = torch.zeros(1, dtype=torch.float64, device=dev)
-    for t in range(cfg.n_iterations):
+    t0 = 0
+    meta = dict(kind="als", m=int(m), n=int(n), k=int(k))
+    if checkpoint and resume and os.path.exists(checkpoint):
+        stc, mt = ck.load_checkpoint(checkpoint)
+        ck.check_meta(mt, **meta)
+        t0, errs = int(mt["iteration"]), stc["errs"].tolist()
+        V = torch.as_tensor(stc["V"], dtype=dtype, device=dev).contiguous()
+        Ul = torch.as_tensor(np.ascontiguousarray(stc["U"][r0:r1]), dtype=dtype, device=dev)
+    for t in range(t0, cfg.n_iterations):
         if fused:
             st = _native.stream_ptr()
             G = g_vv(V, V, allreduce=False)                                    # V is replicated
@@ -140,6 +153,10 @@ def run_als(cfg: ALSConfig, R: Optional[np.ndarray] = None, U0: Optional[np.ndar
         errs.append(err)
         if callback:
             callback(t, err)
+        if checkpoint and checkpoint_every > 0 and ((t + 1) % checkpoint_every == 0 or t + 1 == cfg.n_iterations):
+            U_all = np.concatenate(dist.all_gather_object(Ul.double().cpu().numpy()), axis=0)
+            if dist.is_main:
+                ck.save_checkpoint(checkpoint, dict(U=U_all, V=V, errs=np.asarray(errs)), dict(meta, iteration=t + 1))
     parts = dist.all_gather_object(Ul.double().cpu().numpy())
     return ALSResult(np.concatenate(parts, axis=0), V.double().cpu().numpy(), errs)
 

@@ -10,6 +10,7 @@ damping + all-gather push in one launch per iteration).
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import Dict, Iterable, Optional, Tuple
 
@@ -21,6 +22,7 @@ from ..config import PageRankConfig
 from ..oracle.algorithms import pagerank_oracle
 from ..parallel.dist import Dist, current
 from ..parallel.partition import vertex_range
+from ..utils import checkpoint as ck
 from ..utils.trace import span
 
 
@@ -127,6 +129,7 @@ class ShardedPageRank:
     def reset(self):
         g = self.g
         self.it = 0
+        self._skip_from = 2               # rows without in-edges may be skipped once both parities hold their zeros
         r0 = 1.0 / self.n
         if self.backend == "fused":
             if self.region.epoch % 2:
@@ -144,6 +147,32 @@ class ShardedPageRank:
             self.c = self._gather(r0 * self.inv)
         io = g.inv_outdeg.to(self.dtype)
         self.ranks_local = torch.where(io > 0, torch.full_like(io, r0), torch.zeros_like(io))
+
+    def state_dict(self) -> dict:
+        """Owned slice of the rank vector + iteration counter (rank-local: one file per rank, or gather first)."""
+        self.finish()
+        return {"ranks_local": self.ranks_local.detach().cpu().numpy(), "it": np.int64(self.it),
+                "v0": np.int64(self.g.v0), "v1": np.int64(self.g.v1)}
+
+    def load_state_dict(self, st: dict):
+        """Restore after :meth:`state_dict`: the per-source contributions r/outdeg every rank reads are rebuilt from
+        the restored slices (one all-gather; collective -- every rank must call it)."""
+        if int(st["v0"]) != self.g.v0 or int(st["v1"]) != self.g.v1:
+            raise ValueError("checkpoint was written for a different vertex range / world size")
+        dev = self.ranks_local.device
+        self.ranks_local = torch.as_tensor(np.asarray(st["ranks_local"]), dtype=self.ranks_local.dtype, device=dev)
+        self.it = int(st["it"])
+        self._skip_from = self.it + 2
+        if self.backend == "fused":
+            self.finish()
+            if self.region.epoch % 2:
+                self.region.epoch += 1
+            c = self._gather(self.ranks_local.float() * self.g.inv_outdeg)
+            self.heap.tensor(self.region, (2, self.g.V), torch.float32)[0].copy_(c)     # parity read by the next step
+            self._first = True
+            self.finish()
+        else:
+            self.c = self._gather(self.ranks_local.to(self.dtype) * self.inv)
 
     def _gather(self, loc: torch.Tensor) -> torch.Tensor:
         if self.dist.world == 1:
@@ -168,7 +197,7 @@ class ShardedPageRank:
                 self.heap.comm_ref(), g.row_ptr.data_ptr(), g.col_idx.data_ptr(), g.inv_outdeg.data_ptr(),
                 g.blocks.data_ptr(), g.blocks.numel() - 1, self.nv, g.v0, g.V,
                 base, damp, self.ranks_local.data_ptr(), self.region.payload_off, self.region.flag_base,
-                self.region.next_epoch(), self.ticket.data_ptr(), 0 if self._first else 1, int(self.it >= 2 and self.skip_empty), self.grid,
+                self.region.next_epoch(), self.ticket.data_ptr(), 0 if self._first else 1, int(self.it >= self._skip_from and self.skip_empty), self.grid,
                 _native.stream_ptr()), "pagerank_step")
             self._first = False
         else:
@@ -193,9 +222,11 @@ class ShardedPageRank:
 
 
 def run_pagerank(edges: Iterable[Tuple[int, int]], cfg: PageRankConfig, backend: str = "auto",
-                 dist: Optional[Dist] = None) -> Dict[int, float]:
+                 dist: Optional[Dist] = None, checkpoint: Optional[str] = None, checkpoint_every: int = 0,
+                 resume: bool = False) -> Dict[int, float]:
     """Rank the vertices of an edge list with arbitrary integer ids; returns {vertex: rank} for the
-    vertices the reference would print (those that still hold a rank)."""
+    vertices the reference would print (those that still hold a rank).  With ``checkpoint`` every rank writes its
+    slice to ``<checkpoint>.rank<r>`` every ``checkpoint_every`` iterations and ``resume`` continues from there."""
     if backend == "auto":
         backend = "fused" if _native.available() else "torch"
     edges = [(int(a), int(b)) for a, b in edges]
@@ -208,7 +239,17 @@ def run_pagerank(edges: Iterable[Tuple[int, int]], cfg: PageRankConfig, backend:
     dst = torch.tensor([remap[b] for _, b in edges], dtype=torch.int64, device=dist.device)
     g = build_sharded_graph(src, dst, len(ids), dist)
     pr = ShardedPageRank(g, cfg, dist, backend="fused" if backend == "fused" else "nccl", dtype=torch.float64)
-    for _ in range(cfg.n_iterations):
+    path = None if checkpoint is None else ck.rank_path(checkpoint, dist.rank)
+    meta = dict(kind="pagerank", V=len(ids), n_edges=int(g.n_edges), world=int(dist.world))
+    if path and resume:
+        have = all(dist.all_gather_object(os.path.exists(path)))
+        if have:
+            st, m = ck.load_checkpoint(path)
+            ck.check_meta(m, **meta)
+            pr.load_state_dict(st)
+    while pr.it < cfg.n_iterations:
         pr.step()
+        if path and checkpoint_every > 0 and (pr.it % checkpoint_every == 0 or pr.it == cfg.n_iterations):
+            ck.save_checkpoint(path, pr.state_dict(), dict(meta, iteration=pr.it))
     r = pr.ranks().double().cpu().numpy()
     return {ids[i]: float(r[i]) for i in range(len(ids)) if r[i] > 0}

@@ -21,7 +21,20 @@ def base_parser(description: str) -> argparse.ArgumentParser:
     ap.add_argument("--device", default=None, choices=[None, "cpu", "cuda"])
     ap.add_argument("--quiet", action="store_true", help="suppress per-iteration prints")
     ap.add_argument("--no-save", action="store_true", help="do not write result files")
+    ap.add_argument("--checkpoint", default=None, metavar="FILE.npz",
+                    help="iterative drivers: file that receives the optimiser state (utils/checkpoint.py)")
+    ap.add_argument("--checkpoint-every", type=int, default=0, metavar="K", help="write --checkpoint every K iterations")
+    ap.add_argument("--resume", action="store_true", help="continue from --checkpoint if it exists")
     return ap
+
+
+def checkpoint_kwargs(args) -> dict:
+    """The three checkpoint flags as keyword arguments of the ``run_*`` drivers."""
+    if not args.checkpoint:
+        if args.resume or args.checkpoint_every:
+            raise SystemExit("--resume / --checkpoint-every need --checkpoint FILE")
+        return {}
+    return dict(checkpoint=args.checkpoint, checkpoint_every=args.checkpoint_every, resume=args.resume)
 
 
 def setup(args):

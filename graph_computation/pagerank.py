@@ -36,7 +36,7 @@ def main(argv=None):
     else:
         links = PAGERANK_TOY
     cfg = PageRankConfig(n_slices=n_slices, n_iterations=args.n_iterations, q=args.q)
-    ranks = run_pagerank(links, cfg, backend=args.backend, dist=dist)
+    ranks = run_pagerank(links, cfg, backend=args.backend, dist=dist, **cli.checkpoint_kwargs(args))
     if not args.quiet or len(ranks) <= 64:
         for vertex, rank in ranks.items():
             cli.main_print(dist, "%s has rank: %s." % (vertex, rank))

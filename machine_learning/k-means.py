@@ -37,7 +37,7 @@ def main(argv=None):
     else:
         matrix = KMEANS_TOY
     cfg = KMeansConfig(k=args.k, convergeDist=convergeDist, n_slices=args.n_slices, n_iterations=args.n_iterations)
-    res = run_kmeans(matrix, cfg, backend=args.backend, dist=dist)
+    res = run_kmeans(matrix, cfg, backend=args.backend, dist=dist, **cli.checkpoint_kwargs(args))
     k_centers = [c for c in res.centers]
     cli.main_print(dist, "Final centers: " + str(k_centers))
     if (dist is None or dist.is_main) and not args.no_save:

@@ -32,7 +32,7 @@ def main(argv=None):
     dist = cli.setup(args) if args.backend != "oracle" else None
 
     cfg = ALSConfig(lam=lam, m=args.m, n=args.n, k=args.k, n_iterations=args.n_iterations, n_slices=n_slices, seed=args.seed)
-    res = run_als(cfg, backend=args.backend, dist=dist,
+    res = run_als(cfg, backend=args.backend, dist=dist, **cli.checkpoint_kwargs(args),
                   callback=lambda t, error: cli.main_print(dist, "iterations: %d, rmse: %f" % (t, error)))
     if (dist is None or dist.is_main) and not args.no_save:
         report.save_result("matrix_decomposition_result", args.out_dir, U=res.U, V=res.V, rmse=res.rmse)

@@ -41,7 +41,7 @@ def main(argv=None):
     init = LogisticInit.draw("bmuf", data.dim, cfg.n_slices, args.seed)
     cli.main_print(dist, "Initial w: " + str(init.w))
 
-    res = run_logistic(data, cfg, init, backend=args.backend, dist=dist)
+    res = run_logistic(data, cfg, init, backend=args.backend, dist=dist, **cli.checkpoint_kwargs(args))
     if not args.quiet:
         for t, acc in enumerate(res.accs):
             cli.main_print(dist, "On iteration %d" % (t + 1))

@@ -360,3 +360,62 @@ def test_entry_scripts_run_fused(tmp_path):
                           "--out-dir", str(tmp_path), "--quiet"], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr[-2000:]
     assert "Final acc: " in out.stdout and "Initial w: " in out.stdout
+
+
+# ------------------------------------------------------------------------------------------ checkpoint / resume
+def test_engine_state_dict_resume_fused(dist, tmp_path):
+    """Fused engines: save after a few steps, restore into a FRESH engine, continue -> same state as never stopping."""
+    from distributed_algorithm_pyspark_b200.config import LogisticConfig, PageRankConfig
+    from distributed_algorithm_pyspark_b200.models.kmeans import ShardedKMeans
+    from distributed_algorithm_pyspark_b200.models.logistic import ShardedLogisticEngine
+    from distributed_algorithm_pyspark_b200.models.pagerank import ShardedPageRank, build_sharded_graph
+    from distributed_algorithm_pyspark_b200.utils import checkpoint as ck
+    torch.manual_seed(0)
+    X = torch.randn(20000, 64, device=DEV)
+    y = (torch.rand(20000, device=DEV) < 0.5).float()
+    for algo in ("ssgd", "bmuf", "easgd"):
+        cfg = LogisticConfig.for_algo(algo, seed=1)
+        a = ShardedLogisticEngine(X, y, cfg, dist=dist)
+        for _ in range(7):
+            a.step()
+        b = ShardedLogisticEngine(X, y, cfg, dist=dist)
+        for _ in range(3):
+            b.step()
+        p = str(tmp_path / f"{algo}.npz")
+        ck.save_checkpoint(p, b.state_dict(), {"kind": algo})
+        c = ShardedLogisticEngine(X, y, cfg, dist=dist)
+        c.load_state_dict(ck.load_checkpoint(p)[0])
+        for _ in range(4):
+            c.step()
+        assert c.t == a.t and torch.equal(c.w, a.w) and torch.equal(c.w_local, a.w_local), algo
+
+    pts = torch.randn(5000, 16, device=DEV)
+    c0 = pts[:8].clone()
+    a = ShardedKMeans(pts, 8, c0, dist=dist)
+    for _ in range(5):
+        a.step()
+    b = ShardedKMeans(pts, 8, c0, dist=dist)
+    b.step(); b.step()
+    c = ShardedKMeans(pts, 8, torch.zeros_like(c0), dist=dist)
+    c.load_state_dict(b.state_dict())
+    for _ in range(3):
+        c.step()
+    assert c.iteration == 5 and torch.equal(c.centers, a.centers)
+
+    g = torch.Generator(device="cpu").manual_seed(5)
+    src = torch.randint(0, 3000, (20000,), generator=g).to(DEV)
+    dst = torch.randint(0, 3000, (20000,), generator=g).to(DEV)
+    gr = build_sharded_graph(src, dst, 3000, dist)
+    a = ShardedPageRank(gr, PageRankConfig(), dist)
+    for _ in range(8):
+        a.step()
+    ra = a.ranks().clone()
+    b = ShardedPageRank(gr, PageRankConfig(), dist)
+    for _ in range(5):
+        b.step()
+    st = b.state_dict()
+    b.reset()                                  # fresh state in the same symmetric region, then restore
+    b.load_state_dict(st)
+    for _ in range(3):
+        b.step()
+    assert b.it == 8 and torch.equal(b.ranks(), ra)
