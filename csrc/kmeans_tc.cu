@@ -4,25 +4,39 @@
 // ref math: machine_learning/k-means.py:20-28 (argmin_c ||x - c||, ties -> lowest index) and :57-63
 // (per-cluster vector sum and count).  argmin_c ||x - c||^2 == argmin_c (||c||^2 - 2 x.c); the cross term
 // for a 128-row tile against 128 centroids is one bf16 `tcgen05.mma` chain (M=128, N=128, K=d) whose fp32
-// accumulator lives in TMEM, the centroid operand holds -2c and ||c||^2 is added in the epilogue.
+// accumulator lives in TMEM.  The centroid operand holds -2c, and the accumulator is PRE-LOADED (tcgen05.st) with
+// ||c_j||^2 + C1 in column j, so the tensor core itself delivers the biased distance C1 + ||c||^2 - 2 x.c.
+// C1 = 1.5 * 2^E is chosen (dapb_kmeans_tc_prepare, Cauchy-Schwarz bound from max ||x||^2 and max ||c||^2) so that
+// every biased distance lies in [2^E, 2^(E+1)): one common exponent, i.e. the bit patterns are fixed-point numbers
+// and key = bits * 32 + column-in-group orders like (distance, column) in unsigned arithmetic.  The epilogue is
+// then one IMAD (FMA pipe) per distance and half a 3-input integer min (ALU pipe).
 //
 // Persistent, warp-specialised, one CTA per SM (512 threads):
-//   warp 0   three producer lanes: lane 0 TMA of 128-row tiles of X (HBM -> smem, 128B swizzle, ring of 5 slots),
-//            lane 1 TMA of 128-centroid chunks of the prepared operand (L2 -> smem, 2 stages), lane 2 ||c||^2 ring
-//   warps 1,3  MMA issuers : for each super tile (4 row tiles) x each centroid chunk: 8 x tcgen05.mma per row tile;
-//            warp 1 issues row tiles 0 and 2, warp 3 row tiles 1 and 3
+//   warp 0   three producer lanes: lane 0 TMA of 128-row tiles of X (HBM -> smem, 128B swizzle, 4 slots = one super
+//            tile), lane 1 TMA of 128-centroid chunks of the prepared operand (L2 -> smem, 3 stages: with 2 the
+//            ~1.5 us L2 latency of a 32 KB chunk was exposed once the epilogue got cheaper), lane 2 biased-norm ring
+//   warps 1,3  MMA issuers : for each super tile (4 row tiles) x each centroid chunk: 8 x tcgen05.mma per row tile,
+//            all accumulating; warp 1 issues row tiles 0 and 2, warp 3 row tiles 1 and 3
 //   warp 2   TMEM allocator (512 columns = 4 accumulator buffers of 128 columns)
-//   warps 4-7 and 12-15  arg-min epilogue (row tiles 0-1 / 2-3 of the super tile) : tcgen05.ld (32 columns at a time, next load in flight while the current
-//              one is reduced) -> + ||c||^2 (smem ring fed by warp 2) -> value with the column-in-group index in its 5 low mantissa
-//              bits -> running min per row; a TMEM buffer is released as soon as it is in registers
+//   warps 4-7 and 12-15  arg-min epilogue (row tiles 0-1 / 2-3 of the super tile) : tcgen05.ld (32 columns at a time,
+//            next load in flight while the current one is reduced); the 32 columns just drained are re-initialised
+//            with the NEXT chunk's biased norms (smem ring -> registers -> tcgen05.st) and the buffer goes back to
+//            the MMA issuer after the fourth part
 //   warps 8-11 scatter : red.global.add.v4.f32 of every row (re-read from L2) into sums[assignment], counts += 1
 // A super tile keeps 4 row tiles resident while all centroid chunks stream through, so the centroid operand
 // is re-read from L2 once per 512 rows.  N = 128 per MMA keeps the shared-memory operand traffic
 // ((M + N) * 32 B per 64-cycle MMA = 128 B/clk) within the SM's shared-memory bandwidth; N = 64 was measured
-// at 59 cycles per MMA instead of 32.
+// at 59 cycles per MMA instead of 32.  The last super tile is always processed in full (tiles beyond the data
+// re-read the last tile, outputs are masked).
 //
-// Near-ties: packing the index costs 5 mantissa bits (relative 2^-18 of the value), far below the error already
-// introduced by bf16 inputs; exact tie semantics need the CUDA-core path (kmeans.cu).
+// What bounds it: every distance must leave TMEM as 4 bytes, and TMEM reads run at ~64 B/clk per SM
+// (B300_MICROARCH.md "LDTM throughput"): a 128 x 1024 tile is 512 KB = 8192 cycles of tcgen05.ld against 4096 cycles
+// of MMA (K is only 128).  Three different epilogue instruction mixes (88, 88 and 62 instructions per 32 columns)
+// all measured 7700-7900 cycles per tile -- the kernel sits on that TMEM-read roofline, and the cheaper epilogue
+// pays off only through the power budget (higher sustained clock: 36.7 -> 34.4 ms per iteration on 125M x 128).
+//
+// Near-ties: distances are compared at a resolution of 2^(E-23) <= 4 M * 2^-23 (M = bound on |distance|), far below
+// the error already introduced by bf16 inputs; exact tie semantics need the CUDA-core path (kmeans.cu).
 #include "tc_common.cuh"
 
 using namespace dapb;
@@ -33,12 +47,12 @@ namespace {
 constexpr int kTM = 128;          // rows per tile (UMMA M)
 constexpr int kNB = 128;          // centroids per chunk (UMMA N)
 constexpr int kSuper = 4;         // row tiles per super tile
-constexpr int kASlots = 5;
-constexpr int kBStages = 2;
+constexpr int kASlots = 4;
+constexpr int kBStages = 3;
 constexpr int kTBufs = 4;         // TMEM accumulator buffers (4 x 128 columns = 512)
 constexpr int kThreads = 512;        // 16 warps: 4 service warps, 2 x 4 arg-min warps, 4 scatter warps
 constexpr int kParts = kNB / 32;  // 32-column epilogue steps per accumulator
-constexpr int kCnStages = 2;      // ring of centroid-norm chunks in shared memory (indexed constant loads were 3x slower)
+constexpr int kCnStages = 2;      // ring of biased centroid-norm chunks in shared memory (source of the tcgen05.st pre-load)
 
 template <int KD>
 struct SmemLayout {
@@ -65,7 +79,7 @@ struct KmTcArgs {
   int* assign;            // [n] or null
   long long* dbg;         // optional [64] cycle counters written by CTA 0 (profiling aid), or null
   uint32_t smem_bytes;    // dynamic shared memory actually provided
-  uint32_t keep_mask;     // 0xffffffe0, passed at run time so that (x & mask) | idx stays ONE lop3
+  uint32_t key_mul;       // 32, passed at run time so that bits * 32 + idx stays ONE IMAD (FMA pipe) instead of LEA/LOP3
 };
 
 // cycle accounting for the profiling aid: adds the cycles spent in stmt to acc when dbg is set
@@ -132,13 +146,13 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       uint32_t g = 0;                                    // tiles loaded by this CTA so far
       for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
         const int64_t tile0 = s * kSuper;
-        const int nt = (int)min((int64_t)kSuper, n_tiles - tile0);
+        constexpr int nt = kSuper;            // the last super tile is processed in full, rows beyond n are masked
         for (int t = 0; t < nt; ++t, ++g) {
           const uint32_t slot = g % kASlots, use = g / kASlots;
           DAPB_T(pc0, mbar_wait(&a_empty[slot], (use & 1) ^ 1));
           mbar_arrive_expect_tx(&a_full[slot], L::kATile);
           uint8_t* dst = smem + L::kAOff + slot * L::kATile;
-          const int row0 = (int)((tile0 + t) * kTM);
+          const int row0 = (int)(min(tile0 + t, n_tiles - 1) * kTM);   // tiles beyond the data re-read the last one
 #pragma unroll
           for (int h = 0; h < L::kHalves; ++h)          // default L2 policy: the scatter warps re-read these rows
             tma_load_2d(dst + h * (kTM * 128), &map_x, &a_full[slot], h * 64, row0);
@@ -189,7 +203,7 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       const int64_t n_super_mma = lane == 0 ? n_super : 0;
       for (int64_t s = blockIdx.x; s < n_super_mma; s += gridDim.x) {
         const int64_t tile0 = s * kSuper;
-        const int nt = (int)min((int64_t)kSuper, n_tiles - tile0);
+        constexpr int nt = kSuper;            // the last super tile is processed in full, rows beyond n are masked
         for (int c = 0; c < n_chunks; ++c, ++j) {
           const uint32_t st = j % kBStages;
           DAPB_T(pc0, mbar_wait(&b_full[st], (j / kBStages) & 1));
@@ -198,7 +212,7 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const uint32_t q = q0 + (uint32_t)(c * nt + t);
             if (c == 0) DAPB_T(pc1, mbar_wait(&a_full[slot], (g / kASlots) & 1));
             const uint32_t buf = q % kTBufs;
-            DAPB_T(pc2, mbar_wait(&t_empty[buf], ((q / kTBufs) & 1) ^ 1));
+            DAPB_T(pc2, mbar_wait(&t_empty[buf], (q / kTBufs) & 1));   // pre-loaded with the biased norms
             tc_fence_after();
             // descriptors differ only in the 14-bit start-address field: build the two bases once per step and
             // add compile-time offsets (units of 16 bytes) for the K halves / K steps
@@ -211,7 +225,7 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 #pragma unroll
                 for (int ks = 0; ks < 4; ++ks)
                   umma_bf16(d_tmem, da0 + (uint64_t)((h * (kTM * 128) + ks * 32) >> 4),
-                            db0 + (uint64_t)((h * (kNB * 128) + ks * 32) >> 4), idesc, (h | ks) != 0);
+                            db0 + (uint64_t)((h * (kNB * 128) + ks * 32) >> 4), idesc, 1u);
             });
             DAPB_T(pc4, {
               umma_commit(&t_full[buf]);
@@ -235,8 +249,8 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     const int t_lo = grp * 2;                             // first row tile of this group
     const int row = qd * 32 + lane;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(qd * 32) << 16);
-    const uint32_t keep = a.keep_mask;
-    uint32_t g0 = 0, q0 = 0, jc = 0;                      // tiles / accumulators / chunks before this super tile
+    const uint32_t kmul = a.key_mul;
+    uint32_t g0 = 0, q0 = 0, ji = 0;                      // tiles / accumulators before this super tile; norm chunks used
     uint32_t vA[32], vB[32];
 
     auto issue_load = [&](uint32_t qq, int part, uint32_t* v) {
@@ -247,33 +261,44 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       }
       tmem_ld_32x32b_x32(lane_addr + buf * kNB + part * 32, v);
     };
-    auto finish_load = [&](uint32_t qq, int part) {       // after the last part the accumulator buffer is free
-      DAPB_T(pc1, tmem_ld_wait());
-      if (part == kParts - 1) {
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&t_empty[qq % kTBufs]);
+    // Accumulators are PRE-LOADED with the biased norms ||c_j||^2 + C1 of the chunk they will receive next (all rows of
+    // a column hold the same value) and every MMA accumulates, so what comes back from TMEM already is
+    // C1 + ||c||^2 - 2 x.c: no norm add, no shared-memory operand in the reduction.  The 32 columns a tcgen05.ld has
+    // just drained are re-initialised at once by the same warp (its own 32 TMEM lanes).
+    auto init_part = [&](uint32_t buf, int part, const float* cnx) {
+      const uint4* c4 = reinterpret_cast<const uint4*>(cnx + part * 32);
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        uint32_t w[16];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint4 t = c4[hh * 4 + i];
+          w[4 * i] = t.x; w[4 * i + 1] = t.y; w[4 * i + 2] = t.z; w[4 * i + 3] = t.w;
+        }
+        tmem_st_32x32b_x16(lane_addr + buf * kNB + part * 32 + hh * 16, w);
       }
     };
-    // value | (column within this 32-column group) in the 5 low mantissa bits, ONE lop3 per element
-    // ((x & mask) | imm, LUT 0xEA); which group won is tracked per row
-#define DAPB_PACK(dst, x, J) asm("lop3.b32 %0, %1, %2, " #J ", 0xEA;" : "=r"(dst) : "r"(__float_as_uint(x)), "r"(keep))
-    auto reduce = [&](const uint32_t* v, const float* cn, int group, float m, int& m_group) -> float {
-      const float4* cn4 = reinterpret_cast<const float4*>(cn);
-      float hm = 3.0e38f;
-#ifdef DAPB_KM_EXPERIMENT_NOCN
-#define DAPB_KM_CN(JJ) make_float4(1.f, 2.f, 3.f, 4.f)
-#else
-#define DAPB_KM_CN(JJ) cn4[JJ]
-#endif
+    auto release_buf = [&](uint32_t buf) {                // initialised (or simply drained): hand it to the MMA issuer
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&t_empty[buf]);
+    };
+    // The prepared norms carry a bias C1 = 1.5 * 2^E that puts every biased distance C1 + ||c||^2 - 2 x.c into the
+    // binade [2^E, 2^(E+1)) (dapb_kmeans_tc_prepare chooses E from the Cauchy-Schwarz bound), so the bit patterns
+    // are fixed-point numbers with a common exponent and key = bits * 32 + column is ordered like (distance, column)
+    // in unsigned arithmetic (the 5 bits shifted out are constant).  One IMAD per element on the FMA pipe and half
+    // a 3-input integer min on the ALU pipe; which 32-column group won is tracked per row.
+#define DAPB_PACK(dst, x, J) asm("mad.lo.u32 %0, %1, %2, " #J ";" : "=r"(dst) : "r"(x), "r"(kmul))
+    auto reduce = [&](const uint32_t* v, int group, uint32_t m, int& m_group) -> uint32_t {
+      uint32_t hm = 0xffffffffu;
 #define DAPB_RED4(JJ, J0, J1, J2, J3) {                                          \
-        const float4 c4 = DAPB_KM_CN(JJ);                                        \
         uint32_t p0, p1, p2, p3;                                                 \
-        DAPB_PACK(p0, __uint_as_float(v[JJ * 4 + 0]) + c4.x, J0);                \
-        DAPB_PACK(p1, __uint_as_float(v[JJ * 4 + 1]) + c4.y, J1);                \
-        DAPB_PACK(p2, __uint_as_float(v[JJ * 4 + 2]) + c4.z, J2);                \
-        DAPB_PACK(p3, __uint_as_float(v[JJ * 4 + 3]) + c4.w, J3);                \
-        hm = fminf(fminf(hm, __uint_as_float(p0)), fminf(__uint_as_float(p1), fminf(__uint_as_float(p2), __uint_as_float(p3)))); }
+        DAPB_PACK(p0, v[JJ * 4 + 0], J0);                                        \
+        DAPB_PACK(p1, v[JJ * 4 + 1], J1);                                        \
+        DAPB_PACK(p2, v[JJ * 4 + 2], J2);                                        \
+        DAPB_PACK(p3, v[JJ * 4 + 3], J3);                                        \
+        hm = min(min(hm, p0), min(p1, min(p2, p3))); }
       DAPB_RED4(0, 0, 1, 2, 3) DAPB_RED4(1, 4, 5, 6, 7) DAPB_RED4(2, 8, 9, 10, 11) DAPB_RED4(3, 12, 13, 14, 15)
       DAPB_RED4(4, 16, 17, 18, 19) DAPB_RED4(5, 20, 21, 22, 23) DAPB_RED4(6, 24, 25, 26, 27) DAPB_RED4(7, 28, 29, 30, 31)
 #undef DAPB_RED4
@@ -281,73 +306,67 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       return m;
     };
 
-    for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
+    // number of super tiles of this CTA (all are processed as FULL super tiles: rows beyond n are masked on output)
+    const int64_t my_super = n_super > blockIdx.x ? (n_super - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    if (my_super > 0) {                                   // prologue: first two accumulators of this group <- chunk 0
+      mbar_wait(&cn_full[0], 0);
+      for (int tt = 0; tt < 2; ++tt) {
+        for (int part = 0; part < kParts; ++part) init_part(t_lo + tt, part, cn_s);
+        release_buf(t_lo + tt);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&cn_empty[0]);
+      ji = 1;
+    }
+    int64_t s_idx = 0;
+    for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x, ++s_idx) {
       const int64_t tile0 = s * kSuper;
-      const int nt = (int)min((int64_t)kSuper, n_tiles - tile0);
-      float best[2] = {3.0e38f, 3.0e38f};
-      int bgrp[2] = {0, 0};
-      // accumulator index of (chunk c, row tile t) in this super tile: q0 + c * nt + t
-      if (nt == kSuper) {
-        issue_load(q0 + t_lo, 0, vA);
-        for (int c = 0; c < n_chunks; ++c, ++jc) {
-          const uint32_t cst = jc % kCnStages;
-          mbar_wait(&cn_full[cst], (jc / kCnStages) & 1);
-          const float* cn = cn_s + cst * kNB;
-#pragma unroll
-          for (int tt = 0; tt < 2; ++tt) {
-            const uint32_t qq = q0 + c * kSuper + t_lo + tt;
-            // the accumulator that follows (c, t_lo + 1) for this group is (c + 1, t_lo)
-            const uint32_t qn = tt == 0 ? qq + 1 : qq + kSuper - 1;
-            const bool has_next = tt == 0 || c + 1 < n_chunks;
-            finish_load(qq, 0); issue_load(qq, 1, vB);
-            best[tt] = reduce(vA, cn, c * kParts + 0, best[tt], bgrp[tt]);
-            finish_load(qq, 1); issue_load(qq, 2, vA);
-            best[tt] = reduce(vB, cn + 32, c * kParts + 1, best[tt], bgrp[tt]);
-            finish_load(qq, 2); issue_load(qq, 3, vB);
-            best[tt] = reduce(vA, cn + 64, c * kParts + 2, best[tt], bgrp[tt]);
-            finish_load(qq, 3);
-            if (has_next) issue_load(qn, 0, vA);
-            best[tt] = reduce(vB, cn + 96, c * kParts + 3, best[tt], bgrp[tt]);
-          }
+      uint32_t best0 = 0xffffffffu, best1 = 0xffffffffu;
+      int bgrp0 = 0, bgrp1 = 0;
+      // accumulator index of (chunk c, row tile t) in this super tile: q0 + c * kSuper + t, TMEM buffer = t
+      issue_load(q0 + t_lo, 0, vA);
+      for (int c = 0; c < n_chunks; ++c) {
+        // the accumulator that follows (c, t) in buffer t is (c + 1, t), or (0, t) of the next super tile
+        const bool has_init = c + 1 < n_chunks || s_idx + 1 < my_super;
+        const uint32_t cst = ji % kCnStages;
+        if (has_init) mbar_wait(&cn_full[cst], (ji / kCnStages) & 1);
+        const float* cnx = cn_s + cst * kNB;
+        auto drain = [&](const int tt, uint32_t& bst, int& bg) {
+          const uint32_t qq = q0 + c * kSuper + t_lo + tt, buf = qq % kTBufs;
+          const uint32_t qn = tt == 0 ? qq + 1 : qq + kSuper - 1;
+          const bool has_next = tt == 0 || c + 1 < n_chunks;
+          DAPB_T(pc1, tmem_ld_wait()); if (has_init) init_part(buf, 0, cnx); issue_load(qq, 1, vB);
+          bst = reduce(vA, c * kParts + 0, bst, bg);
+          DAPB_T(pc1, tmem_ld_wait()); if (has_init) init_part(buf, 1, cnx); issue_load(qq, 2, vA);
+          bst = reduce(vB, c * kParts + 1, bst, bg);
+          DAPB_T(pc1, tmem_ld_wait()); if (has_init) init_part(buf, 2, cnx); issue_load(qq, 3, vB);
+          bst = reduce(vA, c * kParts + 2, bst, bg);
+          DAPB_T(pc1, tmem_ld_wait()); if (has_init) { init_part(buf, 3, cnx); release_buf(buf); }
+          if (has_next) issue_load(qn, 0, vA);
+          bst = reduce(vB, c * kParts + 3, bst, bg);
+        };
+        drain(0, best0, bgrp0);
+        drain(1, best1, bgrp1);
+        if (has_init) {
           __syncwarp();
-          if (lane == 0) mbar_arrive(&cn_empty[cst]);     // this warp is done with the chunk's norms
-        }
-      } else {                                            // ragged last super tile: simple path
-        for (int c = 0; c < n_chunks; ++c, ++jc) {
-          const uint32_t cst = jc % kCnStages;
-          mbar_wait(&cn_full[cst], (jc / kCnStages) & 1);
-          const float* cn = cn_s + cst * kNB;
-#pragma unroll
-          for (int tt = 0; tt < 2; ++tt) {
-            if (t_lo + tt < nt) {
-              const uint32_t qq = q0 + c * nt + t_lo + tt;
-#pragma unroll
-              for (int part = 0; part < kParts; ++part) {
-                issue_load(qq, part, vA); finish_load(qq, part);
-                best[tt] = reduce(vA, cn + part * 32, c * kParts + part, best[tt], bgrp[tt]);
-              }
-            }
-          }
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&cn_empty[cst]);
+          if (lane == 0) mbar_arrive(&cn_empty[cst]);     // this warp is done with that chunk's norms
+          ++ji;
         }
       }
 #pragma unroll
       for (int tt = 0; tt < 2; ++tt) {
         const int t = t_lo + tt;
-        if (t < nt) {
-          const uint32_t g = g0 + t, slot = g % kASlots;
-          const int cidx = bgrp[tt] * 32 + (int)(__float_as_uint(best[tt]) & 31u);
-          mbar_wait(&as_empty[slot], ((g / kASlots) & 1) ^ 1);     // scatter warps are done with the previous use
-          assign_s[slot * kTM + row] = (uint16_t)cidx;
-          const int64_t grow = (tile0 + t) * kTM + row;
-          if (a.assign && grow < a.n) a.assign[grow] = cidx;
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&as_full[slot]);
-        }
+        const uint32_t g = g0 + t, slot = g % kASlots;
+        const int cidx = (tt == 0 ? bgrp0 : bgrp1) * 32 + (int)((tt == 0 ? best0 : best1) & 31u);
+        mbar_wait(&as_empty[slot], ((g / kASlots) & 1) ^ 1);     // scatter warps are done with the previous use
+        assign_s[slot * kTM + row] = (uint16_t)cidx;
+        const int64_t grow = (tile0 + t) * kTM + row;
+        if (a.assign && grow < a.n) a.assign[grow] = cidx;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&as_full[slot]);
       }
-      g0 += nt;
-      q0 += (uint32_t)(n_chunks * nt);
+      g0 += kSuper;
+      q0 += (uint32_t)(n_chunks * kSuper);
     }
 #undef DAPB_PACK
   } else if (warp >= 8 && warp < 12) {
@@ -356,7 +375,7 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     uint32_t g = 0;
     for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
       const int64_t tile0 = s * kSuper;
-      const int nt = (int)min((int64_t)kSuper, n_tiles - tile0);
+      constexpr int nt = kSuper;
       for (int t = 0; t < nt; ++t, ++g) {
         const uint32_t slot = g % kASlots, par = (g / kASlots) & 1;
         DAPB_T(pc0, mbar_wait(&as_full[slot], par));
@@ -411,7 +430,8 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 }
 
 // centres fp32 [k, d] -> tensor-core operand bf16(-2 c) [k, d] and ||bf16(c)||^2 (the norm of the ROUNDED centre,
-// so that the assignment is the exact nearest neighbour w.r.t. one consistent set of centres)
+// so that the assignment is the exact nearest neighbour w.r.t. one consistent set of centres); cnorm[k] receives
+// max_j ||c_j||^2 (as float bits; norms are >= 0 so the integer order is the float order)
 __global__ void kmeans_tc_prep_kernel(const float* __restrict__ C, int k, int d, __nv_bfloat16* __restrict__ Bp,
                                       float* __restrict__ cnorm) {
   const int lane = threadIdx.x & 31;
@@ -425,7 +445,24 @@ __global__ void kmeans_tc_prep_kernel(const float* __restrict__ C, int k, int d,
     Bp[(size_t)c * d + j] = __float2bfloat16(-2.0f * cf);       // exact: power-of-two scaling
   }
   s = warp_sum(s);
-  if (lane == 0) cnorm[c] = s;
+  if (lane == 0) {
+    cnorm[c] = s;
+    atomicMax(reinterpret_cast<int*>(cnorm + k), __float_as_int(s));
+  }
+}
+
+// cnorm[j] += C1 with C1 = 1.5 * 2^E, 2^(E-1) > M >= |x.x - ||x||^2 - 2 x.c + ...| = |cn_j - 2 x.c_j| for every row x
+// and centre j: M = cn_max + 2 sqrt(xn_max * cn_max) (Cauchy-Schwarz) with 1 % slack for the fp32 accumulation.
+// Then C1 + (cn_j - 2 x.c_j) lies in [2^E, 2^(E+1)): one common exponent, resolution 2^(E-23) <= M * 2^-20.
+__global__ void kmeans_tc_bias_kernel(float* __restrict__ cnorm, int k, float xnorm_max) {
+  const float cmax = cnorm[k];
+  const float M = 1.01f * (cmax + 2.0f * sqrtf(xnorm_max * cmax)) + 1e-30f;
+  int e;
+  frexpf(M, &e);                                  // M = f * 2^e, f in [0.5, 1)  =>  M < 2^e
+  const float C1 = ldexpf(1.5f, e + 1);           // E = e + 1: 2^(E-1) = 2^e > M
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < k) cnorm[j] += C1;
+  if (j == 0) cnorm[k + 1] = C1;
 }
 
 template <int KD>
@@ -441,11 +478,17 @@ int launch_km(const CUtensorMap& mx, const CUtensorMap& mc, KmTcArgs a, int grid
 
 }  // namespace
 
+// cnorm: [k + 8] floats (k biased norms, then the running max and the bias, see above); xnorm_max >= max_i ||x_i||^2
+// over every row the assignment kernel will see (a looser bound only costs resolution).
 extern "C" int dapb_kmeans_tc_prepare(const float* centers, int32_t k, int32_t d, void* b_operand, float* cnorm,
-                                      void* stream) {
+                                      float xnorm_max, void* stream) {
   DAPB_REQUIRE(centers && b_operand && cnorm && k >= 1 && d >= 1, "kmeans_tc_prepare: bad arguments");
+  DAPB_REQUIRE(xnorm_max >= 0.f && xnorm_max < 1e30f, "kmeans_tc_prepare: xnorm_max must be a finite bound on ||x||^2");
+  DAPB_CUDA_CHECK(cudaMemsetAsync(cnorm + k, 0, 8 * sizeof(float), (cudaStream_t)stream));
   const int blocks = (k * 32 + 255) / 256;
   kmeans_tc_prep_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(centers, k, d, (__nv_bfloat16*)b_operand, cnorm);
+  DAPB_LAUNCH_CHECK();
+  kmeans_tc_bias_kernel<<<(k + 255) / 256, 256, 0, (cudaStream_t)stream>>>(cnorm, k, xnorm_max);
   DAPB_LAUNCH_CHECK();
   return 0;
 }
@@ -473,7 +516,7 @@ extern "C" int dapb_kmeans_assign_tc_dbg(const void* X, int64_t n, int32_t d, co
   if (rc) return rc;
   rc = make_tensor_map_bf16_2d(&mc, b_operand, (uint64_t)k, (uint64_t)d, (uint64_t)d, 64, kNB);
   if (rc) return rc;
-  KmTcArgs a{(const __nv_bfloat16*)X, n, k, cnorm, sums, counts, assign, dbg, 0, 0xffffffe0u};
+  KmTcArgs a{(const __nv_bfloat16*)X, n, k, cnorm, sums, counts, assign, dbg, 0, 32u};
   if (grid <= 0) grid = dapb::sm_count();
   const int64_t n_super = ((n + kTM - 1) / kTM + kSuper - 1) / kSuper;
   if (grid > n_super) grid = (int)n_super;

@@ -93,7 +93,7 @@ def _declare(lib: C.CDLL):
         "dapb_kmeans_assign": (C.c_int, [vp, i64, i32, i32, vp, i32, vp, vp, vp, vp]),
         "dapb_kmeans_finalize": (C.c_int, [P(DapbComm), vp, vp, vp, i32, i32, i32, u64, u32, u64, vp, i32, vp]),
         "dapb_kmeans_payload_bytes": (u64, [i32, i32, i32, i32]),
-        "dapb_kmeans_tc_prepare": (C.c_int, [vp, i32, i32, vp, vp, vp]),
+        "dapb_kmeans_tc_prepare": (C.c_int, [vp, i32, i32, vp, vp, C.c_float, vp]),
         "dapb_kmeans_assign_tc": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, vp, vp, i32, vp]),
         "dapb_kmeans_assign_tc_dbg": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, vp, vp, i32, vp, vp]),
         "dapb_pagerank_init": (C.c_int, [P(DapbComm), vp, i64, i64, i64, f32, u64, vp]),

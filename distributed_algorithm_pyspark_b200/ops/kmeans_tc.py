@@ -24,12 +24,20 @@ class KMeansTC:
         self.n, self.d = X.shape
         self.grid = grid
         self.b_operand = torch.empty(self.k, self.d, dtype=torch.bfloat16, device=X.device)
-        self.cnorm = torch.empty(self.k, dtype=torch.float32, device=X.device)
+        self.cnorm = torch.empty(self.k + 8, dtype=torch.float32, device=X.device)
+        # max ||x||^2 over the resident shard (X never changes): bounds every distance, so the kernel can compare
+        # fixed-exponent bit patterns instead of floats.  One chunked pass at construction.
+        xmax = 0.0
+        step = max(1, (1 << 28) // max(self.d, 1))
+        for i in range(0, self.n, step):
+            xc = X[i:i + step].float()
+            xmax = max(xmax, float((xc * xc).sum(1).max().item()))
+        self.xnorm_max = xmax
 
     def assign_accumulate(self, centers: torch.Tensor, sums: torch.Tensor, counts: torch.Tensor, assign=None):
         st = _native.stream_ptr()
         _native.check(self.lib.dapb_kmeans_tc_prepare(centers.data_ptr(), self.k, self.d, self.b_operand.data_ptr(),
-                                                      self.cnorm.data_ptr(), st), "kmeans_tc_prepare")
+                                                      self.cnorm.data_ptr(), self.xnorm_max, st), "kmeans_tc_prepare")
         _native.check(self.lib.dapb_kmeans_assign_tc(self.X.data_ptr(), self.n, self.d, self.b_operand.data_ptr(),
                                                      self.cnorm.data_ptr(), self.k, _native.ptr(assign), sums.data_ptr(),
                                                      counts.data_ptr(), self.grid, st), "kmeans_assign_tc")

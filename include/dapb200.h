@@ -175,9 +175,11 @@ DAPB_API int dapb_kmeans_finalize(const DapbComm* comm, void* sums, int32_t* cou
                                   uint64_t epoch, int32_t* counts_out, int32_t clear_partials, void* stream);
 DAPB_API uint64_t dapb_kmeans_payload_bytes(int32_t world, int32_t k, int32_t d, int32_t elem_bytes);
 /* Tensor-core assignment (tcgen05.mma + TMEM + TMA), bf16 points, d in {64,128}, k multiple of 128 <= 1024.
- * dapb_kmeans_tc_prepare turns fp32 centres into the bf16 operand (-2c) [k,d] and ||bf16(c)||^2 [k]. */
+ * dapb_kmeans_tc_prepare turns fp32 centres into the bf16 operand (-2c) [k,d] and the BIASED norms
+ * ||bf16(c)||^2 + C1 in cnorm[0..k) (cnorm holds k + 8 floats; C1 makes all distances share one exponent so that the
+ * arg-min runs on integer keys, see csrc/kmeans_tc.cu).  xnorm_max: an upper bound on ||x||^2 over all rows. */
 DAPB_API int dapb_kmeans_tc_prepare(const float* centers, int32_t k, int32_t d, void* b_operand, float* cnorm,
-                                    void* stream);
+                                    float xnorm_max, void* stream);
 DAPB_API int dapb_kmeans_assign_tc(const void* X, int64_t n, int32_t d, const void* b_operand, const float* cnorm,
                                    int32_t k, int32_t* assign, float* sums, int32_t* counts, int32_t grid,
                                    void* stream);

@@ -8,11 +8,12 @@ n, d, k = int(sys.argv[1]) if len(sys.argv) > 1 else 16_000_000, 128, 1024
 dev = "cuda"
 X = torch.randn(n, d, device=dev).to(torch.bfloat16)
 C = torch.randn(k, d, device=dev)
-B = torch.empty(k, d, dtype=torch.bfloat16, device=dev); cn = torch.empty(k, device=dev)
+B = torch.empty(k, d, dtype=torch.bfloat16, device=dev); cn = torch.empty(k + 8, device=dev)
 sums = torch.zeros(k, d, device=dev); counts = torch.zeros(k, dtype=torch.int32, device=dev)
 dbg = torch.zeros(64, dtype=torch.int64, device=dev)
 st = _native.stream_ptr()
-_native.check(lib.dapb_kmeans_tc_prepare(C.data_ptr(), k, d, B.data_ptr(), cn.data_ptr(), st))
+_native.check(lib.dapb_kmeans_tc_prepare(C.data_ptr(), k, d, B.data_ptr(), cn.data_ptr(),
+                                         float((X[:1 << 20].float() ** 2).sum(1).max().item()) * 1.5, st))
 for rep in range(3):
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()

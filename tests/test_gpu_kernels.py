@@ -400,7 +400,8 @@ def test_engine_state_dict_resume_fused(dist, tmp_path):
     c.load_state_dict(b.state_dict())
     for _ in range(3):
         c.step()
-    assert c.iteration == 5 and torch.equal(c.centers, a.centers)
+    assert c.iteration == 5                     # float atomics: the sums are not bit-reproducible run to run
+    torch.testing.assert_close(c.centers, a.centers, rtol=1e-4, atol=1e-5)
 
     g = torch.Generator(device="cpu").manual_seed(5)
     src = torch.randint(0, 3000, (20000,), generator=g).to(DEV)
