@@ -139,6 +139,135 @@ __global__ void __launch_bounds__(kPrThreads) pagerank_step_kernel(PrArgs a, Dap
   if (tid < c.world) st_release_sys(comm_flags(c, tid) + a.flag_base + c.rank, a.epoch);
 }
 
+// =================================================================================================
+// Warp-granular variant (dapb_pagerank_step_v2).  The CTA-wide kernel above spends ~40 % of its warp time in
+// the two __syncthreads per row block (ncu: stall_barrier) with only 4 gathers in flight per thread.  Here every
+// WARP owns a row block of <= 512 non-zeros: 16 independent gathers per lane are in flight before the first is
+// consumed, the staging buffer is warp-private (__syncwarp only), and warps never wait for each other.
+// Rows too long for that are taken out of the main CSR on the host ("hub" rows, R-MAT has a few thousand):
+// their non-zeros are cut into 2048-element chunks, one warp per chunk writes a partial sum
+// (pagerank_hub_partial_kernel), and one thread per hub row adds the partials IN CHUNK ORDER (deterministic) and
+// runs the same fused epilogue (pagerank_hub_finish_kernel).  Launch order hub partial -> hub finish -> main, so
+// the completion flag published by the main kernel's last CTA covers the hub pushes as well.
+// =================================================================================================
+constexpr int kWarpCap = 512;
+constexpr int kWarpsPerCta = kPrThreads / 32;
+
+__device__ __forceinline__ bool pr_is_hub(const DapbPrHub& h, int32_t row) {
+  int lo = 0, hi = h.n_hub;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    const int32_t v = h.hub_rows[mid];
+    if (v == row) return true;
+    if (v < row) lo = mid + 1; else hi = mid;
+  }
+  return false;
+}
+
+__device__ __forceinline__ void pr_wait_prev(const PrArgs& a, const DapbComm& c) {
+  if (c.world > 1 && a.wait_prev) {                  // all peers' pushes of the previous iteration landed?
+    if (threadIdx.x < (unsigned)c.world) comm_wait_flag(comm_flags(c, c.rank) + a.flag_base + threadIdx.x, a.epoch - 1);
+    __syncthreads();
+  }
+}
+
+// lane-strided sum of c_cur[col[e]] for e in [b0, b1), 8 gathers in flight per lane; result valid on every lane
+__device__ __forceinline__ float pr_warp_row_sum(const float* __restrict__ c_cur, const int32_t* __restrict__ col,
+                                                 int64_t b0, int64_t b1, int lane) {
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  int64_t e = b0 + lane;
+  for (; e + 7 * 32 < b1; e += 8 * 32) {
+    int32_t u[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) u[j] = col[e + j * 32];
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = __ldcg(c_cur + u[j]);
+    s0 += f[0] + f[4]; s1 += f[1] + f[5]; s2 += f[2] + f[6]; s3 += f[3] + f[7];
+  }
+  for (; e < b1; e += 32) s0 += __ldcg(c_cur + col[e]);
+  return warp_sum((s0 + s1) + (s2 + s3));
+}
+
+__global__ void __launch_bounds__(kPrThreads) pagerank_warp_kernel(PrArgs a, DapbPrHub h, DapbComm c) {
+  __shared__ float vals_all[kWarpsPerCta][kWarpCap];
+  __shared__ bool s_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float* vals = vals_all[warp];
+  const float* c_cur = reinterpret_cast<const float*>(comm_payload(c, c.rank, a.c_off)) + (((a.epoch - 1) & 1) * a.V);
+  float* c_next_local = reinterpret_cast<float*>(comm_payload(c, c.rank, a.c_off)) + ((a.epoch & 1) * a.V);
+  pr_wait_prev(a, c);
+
+  const int n_warps = gridDim.x * kWarpsPerCta;
+  for (int blk = blockIdx.x * kWarpsPerCta + warp; blk < a.n_blocks; blk += n_warps) {
+    const int r0 = a.blocks[blk], r1 = a.blocks[blk + 1];
+    if (r0 >= r1) continue;
+    const int64_t e0 = a.row_ptr[r0], e1 = a.row_ptr[r1];
+    if (e1 - e0 <= kWarpCap) {
+      const int nnz = (int)(e1 - e0);
+      const int32_t* ci = a.col_idx + e0;
+      int32_t u[kWarpCap / 32];
+#pragma unroll
+      for (int j = 0; j < kWarpCap / 32; ++j) u[j] = lane + j * 32 < nnz ? ci[lane + j * 32] : -1;
+      float f[kWarpCap / 32];
+#pragma unroll
+      for (int j = 0; j < kWarpCap / 32; ++j) f[j] = u[j] >= 0 ? __ldcg(c_cur + u[j]) : 0.f;   // 16 gathers in flight
+#pragma unroll
+      for (int j = 0; j < kWarpCap / 32; ++j) vals[lane + j * 32] = f[j];
+      __syncwarp();
+      for (int r = r0 + lane; r < r1; r += 32) {
+        const int b0 = (int)(a.row_ptr[r] - e0), b1 = (int)(a.row_ptr[r + 1] - e0);
+        if (b1 == b0 && (a.skip_empty || pr_is_hub(h, r))) continue;   // stays 0 / written by the hub kernels
+        float s = 0.f;
+        for (int j = b0; j < b1; ++j) s += vals[j];
+        pr_finish_row(a, c, c_next_local, r, s);
+      }
+      __syncwarp();
+    } else {                                                            // block with a row of 512 .. hub_threshold non-zeros
+      for (int r = r0; r < r1; ++r) {
+        const int64_t b0 = a.row_ptr[r], b1 = a.row_ptr[r + 1];
+        if (b1 == b0 && (a.skip_empty || pr_is_hub(h, r))) continue;
+        const float s = pr_warp_row_sum(c_cur, a.col_idx, b0, b1, lane);
+        if (lane == 0) pr_finish_row(a, c, c_next_local, r, s);
+      }
+    }
+  }
+
+  // ---- completion: last CTA tells every rank that this rank's slice of iteration `epoch` is in ----
+  __threadfence_system();
+  __syncthreads();
+  if (tid == 0) {
+    unsigned t = atomicAdd(a.ticket, 1u);
+    s_last = (t == gridDim.x - 1);
+    if (s_last) *a.ticket = 0;
+  }
+  __syncthreads();
+  if (!s_last || c.world == 1) return;
+  if (tid == 0) __threadfence_system();
+  __syncthreads();
+  if (tid < c.world) st_release_sys(comm_flags(c, tid) + a.flag_base + c.rank, a.epoch);
+}
+
+__global__ void __launch_bounds__(kPrThreads) pagerank_hub_partial_kernel(PrArgs a, DapbPrHub h, DapbComm c) {
+  const int lane = threadIdx.x & 31;
+  const float* c_cur = reinterpret_cast<const float*>(comm_payload(c, c.rank, a.c_off)) + (((a.epoch - 1) & 1) * a.V);
+  pr_wait_prev(a, c);
+  const int n_warps = gridDim.x * kWarpsPerCta;
+  for (int ch = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5); ch < h.n_chunks; ch += n_warps) {
+    const float s = pr_warp_row_sum(c_cur, h.hub_col, h.chunk_start[ch], h.chunk_end[ch], lane);
+    if (lane == 0) h.chunk_partial[ch] = s;
+  }
+}
+
+__global__ void pagerank_hub_finish_kernel(PrArgs a, DapbPrHub h, DapbComm c) {
+  float* c_next_local = reinterpret_cast<float*>(comm_payload(c, c.rank, a.c_off)) + ((a.epoch & 1) * a.V);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= h.n_hub) return;
+  float s = 0.f;
+  for (int ch = h.hub_chunk_ptr[i]; ch < h.hub_chunk_ptr[i + 1]; ++ch) s += h.chunk_partial[ch];
+  pr_finish_row(a, c, c_next_local, h.hub_rows[i], s);
+}
+
 // contribution vector of iteration 0: c[v] = (1/n) / outdeg[v] for source vertices, written by the
 // owner of v into every rank's buffer 0 (ref pagerank.py:47).
 __global__ void pagerank_init_kernel(DapbComm c, const float* inv_outdeg, int64_t nv_local, int64_t v0, int64_t V,
@@ -182,6 +311,43 @@ extern "C" int dapb_pagerank_step(const DapbComm* comm, const int64_t* row_ptr, 
   if (grid <= 0) grid = dapb::sm_count() * 8;
   if (grid > n_blocks) grid = n_blocks > 0 ? n_blocks : 1;
   pagerank_step_kernel<<<grid, kPrThreads, 0, (cudaStream_t)stream>>>(a, *comm);
+  DAPB_LAUNCH_CHECK();
+  return 0;
+}
+
+// Warp-granular step (see pagerank_warp_kernel): `blocks` must hold row blocks of <= 512 non-zeros + rows built on the
+// CSR WITHOUT the hub rows' non-zeros (hub rows have length 0 there); `hub` describes the hub rows (may be empty).
+extern "C" int dapb_pagerank_step_v2(const DapbComm* comm, const int64_t* row_ptr, const int32_t* col_idx,
+                                     const float* inv_outdeg, const int32_t* blocks, int32_t n_blocks,
+                                     int64_t nv_local, int64_t v0, int64_t V, const DapbPrHub* hub, float base,
+                                     float damp, float* ranks_local, uint64_t c_off, uint32_t flag_base,
+                                     uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t skip_empty,
+                                     int32_t grid, void* stream) {
+  DAPB_REQUIRE(comm && comm->world >= 1 && comm->world <= DAPB_MAX_RANKS, "pagerank_step_v2: bad comm");
+  DAPB_REQUIRE(epoch >= 1 && ticket != nullptr && hub != nullptr, "pagerank_step_v2: epoch starts at 1, ticket and hub required");
+  DAPB_REQUIRE(blocks != nullptr && n_blocks >= 0, "pagerank_step_v2: row blocks required (see build_sharded_graph)");
+  DAPB_REQUIRE(hub->n_hub >= 0 && hub->n_chunks >= 0 && (hub->n_hub == 0 || (hub->hub_rows && hub->hub_col &&
+               hub->chunk_start && hub->chunk_end && hub->hub_chunk_ptr && hub->chunk_partial)),
+               "pagerank_step_v2: incomplete hub description");
+  PrArgs a;
+  a.row_ptr = row_ptr; a.col_idx = col_idx; a.inv_outdeg = inv_outdeg; a.blocks = blocks; a.n_blocks = n_blocks;
+  a.nv_local = nv_local; a.v0 = v0; a.V = V; a.base = base; a.damp = damp; a.ranks_local = ranks_local;
+  a.c_off = c_off; a.flag_base = flag_base; a.epoch = epoch; a.ticket = ticket; a.wait_prev = wait_prev; a.skip_empty = skip_empty;
+  const DapbPrHub h = *hub;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int cap = dapb::sm_count() * 8;
+  if (h.n_hub > 0) {
+    int g1 = (h.n_chunks + kWarpsPerCta - 1) / kWarpsPerCta;
+    if (g1 > cap) g1 = cap;
+    pagerank_hub_partial_kernel<<<g1, kPrThreads, 0, st>>>(a, h, *comm);
+    DAPB_LAUNCH_CHECK();
+    pagerank_hub_finish_kernel<<<(h.n_hub + 127) / 128, 128, 0, st>>>(a, h, *comm);
+    DAPB_LAUNCH_CHECK();
+  }
+  if (grid <= 0) grid = cap;
+  const int need = (n_blocks + kWarpsPerCta - 1) / kWarpsPerCta;
+  if (grid > need) grid = need > 0 ? need : 1;
+  pagerank_warp_kernel<<<grid, kPrThreads, 0, st>>>(a, h, *comm);
   DAPB_LAUNCH_CHECK();
   return 0;
 }

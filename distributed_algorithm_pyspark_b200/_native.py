@@ -25,6 +25,12 @@ class DapbComm(C.Structure):
                 ("heap", C.c_void_p * MAX_RANKS), ("heap_bytes", C.c_uint64)]
 
 
+class DapbPrHub(C.Structure):
+    _fields_ = [("hub_rows", C.c_void_p), ("hub_col", C.c_void_p), ("chunk_start", C.c_void_p),
+                ("chunk_end", C.c_void_p), ("hub_chunk_ptr", C.c_void_p), ("chunk_partial", C.c_void_p),
+                ("n_hub", C.c_int32), ("n_chunks", C.c_int32)]
+
+
 class DapbLrParityArgs(C.Structure):
     _fields_ = [
         ("X", C.c_void_p), ("y", C.c_void_p), ("part_off", C.c_void_p), ("masks", C.c_void_p),
@@ -99,6 +105,8 @@ def _declare(lib: C.CDLL):
         "dapb_pagerank_init": (C.c_int, [P(DapbComm), vp, i64, i64, i64, f32, u64, vp]),
         "dapb_pagerank_step": (C.c_int, [P(DapbComm), vp, vp, vp, vp, i32, i64, i64, i64, f32, f32, vp,
                                          u64, u32, u64, vp, i32, i32, i32, vp]),
+        "dapb_pagerank_step_v2": (C.c_int, [P(DapbComm), vp, vp, vp, vp, i32, i64, i64, i64, P(DapbPrHub), f32, f32, vp,
+                                            u64, u32, u64, vp, i32, i32, i32, vp]),
         "dapb_tc_seed": (C.c_int, [vp, i64, vp, u64, vp, vp, i32, i32, vp]),
         "dapb_tc_expand": (C.c_int, [P(DapbComm), vp, vp, vp, i64, vp, u64, vp, vp, u64, u64, vp]),
         "dapb_tc_exchange": (C.c_int, [P(DapbComm), vp, u64, u64, u32, u64, vp]),

@@ -10,6 +10,7 @@ damping + all-gather push in one launch per iteration).
 """
 from __future__ import annotations
 
+import ctypes as C
 import os
 from dataclasses import dataclass
 from typing import Dict, Iterable, Optional, Tuple
@@ -41,6 +42,68 @@ class ShardedGraph:
     outdeg_local: torch.Tensor   # int64 [nv_local]
     blocks: Optional[torch.Tensor] = None    # int32 [n_blocks + 1] row boundaries of ~block_nnz non-zeros each
     block_nnz: int = 2048
+    hub: Optional["HubRows"] = None          # warp-granular layout: rows too long for one warp (see split_hub_rows)
+
+
+@dataclass
+class HubRows:
+    """Rows with more than ``threshold`` in-edges, taken out of the main CSR (csrc/pagerank.cu, warp-granular variant)."""
+    rows: torch.Tensor            # int32 [n_hub] local row ids, ascending
+    col: torch.Tensor             # int32 source ids of all hub rows, row after row
+    chunk_start: torch.Tensor     # int64 [n_chunks] offsets into col
+    chunk_end: torch.Tensor       # int64 [n_chunks]
+    chunk_ptr: torch.Tensor       # int32 [n_hub + 1] chunks of hub row i
+    partial: torch.Tensor         # float32 [n_chunks] scratch
+    ptr: Optional[torch.Tensor] = None   # int64 [n_hub + 1] offsets of the hub rows in col
+
+    def c_struct(self) -> "_native.DapbPrHub":
+        h = _native.DapbPrHub()
+        h.hub_rows, h.hub_col = self.rows.data_ptr(), self.col.data_ptr()
+        h.chunk_start, h.chunk_end = self.chunk_start.data_ptr(), self.chunk_end.data_ptr()
+        h.hub_chunk_ptr, h.chunk_partial = self.chunk_ptr.data_ptr(), self.partial.data_ptr()
+        h.n_hub, h.n_chunks = int(self.rows.numel()), int(self.chunk_start.numel())
+        return h
+
+
+def split_hub_rows(row_ptr: torch.Tensor, col_idx: torch.Tensor, threshold: int, chunk: int = 2048):
+    """Returns (row_ptr', col_idx', HubRows): the CSR without the non-zeros of rows longer than ``threshold`` (those rows
+    have length 0 in row_ptr') and the description of the removed rows cut into ``chunk``-element pieces."""
+    dev = row_ptr.device
+    lens = row_ptr[1:] - row_ptr[:-1]
+    rows = torch.nonzero(lens > threshold).flatten()
+    i64, i32 = torch.int64, torch.int32
+    if rows.numel() == 0:
+        z = torch.zeros(0, dtype=i64, device=dev)
+        return row_ptr, col_idx, HubRows(z.to(i32), z.to(i32), z, z, torch.zeros(1, dtype=i32, device=dev),
+                                         torch.zeros(0, dtype=torch.float32, device=dev), torch.zeros(1, dtype=i64, device=dev))
+    hs, he = row_ptr[rows], row_ptr[rows + 1]
+    hs_l, he_l = hs.tolist(), he.tolist()
+    hub_col = torch.cat([col_idx[s:e] for s, e in zip(hs_l, he_l)]).contiguous()
+    pieces, prev = [], 0
+    for s, e in zip(hs_l, he_l):
+        if s > prev:
+            pieces.append(col_idx[prev:s])
+        prev = e
+    if prev < col_idx.numel():
+        pieces.append(col_idx[prev:])
+    main_col = torch.cat(pieces).contiguous() if pieces else col_idx[:0].contiguous()
+    lens_main = lens.clone()
+    lens_main[rows] = 0
+    rp = torch.zeros_like(row_ptr)
+    rp[1:] = torch.cumsum(lens_main, 0)
+    hub_len = he - hs
+    hub_ptr = torch.zeros(rows.numel() + 1, dtype=i64, device=dev)
+    hub_ptr[1:] = torch.cumsum(hub_len, 0)
+    nch = (hub_len + chunk - 1) // chunk
+    chunk_ptr = torch.zeros(rows.numel() + 1, dtype=i64, device=dev)
+    chunk_ptr[1:] = torch.cumsum(nch, 0)
+    owner = torch.repeat_interleave(torch.arange(rows.numel(), device=dev), nch)
+    within = torch.arange(owner.numel(), device=dev) - chunk_ptr[owner]
+    c_start = hub_ptr[owner] + within * chunk
+    c_end = torch.minimum(c_start + chunk, hub_ptr[owner + 1])
+    hub = HubRows(rows.to(i32).contiguous(), hub_col, c_start.contiguous(), c_end.contiguous(),
+                  chunk_ptr.to(i32).contiguous(), torch.zeros(owner.numel(), dtype=torch.float32, device=dev), hub_ptr)
+    return rp, main_col, hub
 
 
 def balanced_vertex_bounds(indeg_all: torch.Tensor, world: int, vertex_cost: int = 8):
@@ -60,10 +123,15 @@ def balanced_vertex_bounds(indeg_all: torch.Tensor, world: int, vertex_cost: int
 
 
 def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Optional[Dist] = None,
-                        block_nnz: int = 2048, balance: bool = True) -> ShardedGraph:
+                        block_nnz: Optional[int] = None, balance: bool = True, layout: Optional[str] = None,
+                        hub_threshold: int = 2048, hub_chunk: int = 2048) -> ShardedGraph:
     """De-duplicate (ref pagerank.py:41) and build this rank's CSR(A^T) rows.  ``src``/``dst`` hold the FULL
     edge list on every rank (the generators are deterministic), int64 on the target device."""
     dist = dist or current()
+    if layout is None:                  # "warp": warp-granular kernel + hub rows (default); "cta": CTA-wide row blocks
+        layout = os.environ.get("DAPB_PR_LAYOUT", "warp")
+    if block_nnz is None:
+        block_nnz = 512 if layout == "warp" else 2048
     key = torch.unique(dst.to(torch.int64) * V + src.to(torch.int64))        # sorted by (dst, src)
     d_all = torch.div(key, V, rounding_mode="floor")
     s_all = key - d_all * V
@@ -87,6 +155,10 @@ def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Opti
     # first row whose cumulative cost is >= k * block_nnz, so a block holds <= block_nnz rows AND (unless it
     # contains one very long row) <= block_nnz non-zeros -- the skewed R-MAT degrees are balanced by construction
     nv = v1 - v0
+    col_local = s_loc.to(torch.int32).contiguous()
+    hub = None
+    if layout == "warp":
+        row_ptr, col_local, hub = split_hub_rows(row_ptr, col_local, hub_threshold, hub_chunk)
     nnz = int(row_ptr[-1].item())
     cumw = (row_ptr[:-1] + torch.arange(nv, device=src.device, dtype=torch.int64)).contiguous()
     n_blocks = max(1, (nnz + nv + block_nnz - 1) // block_nnz)
@@ -96,8 +168,8 @@ def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Opti
         starts[0] = 0
     blocks = torch.cat([starts, torch.tensor([nv], device=src.device)]).to(torch.int32).contiguous()
     return ShardedGraph(V=V, n_sources=n_sources, n_edges=n_edges, v0=v0, v1=v1, bounds=bounds, row_ptr=row_ptr,
-                        col_idx=s_loc.to(torch.int32).contiguous(), inv_outdeg=inv.contiguous(), outdeg_local=od,
-                        blocks=blocks, block_nnz=block_nnz)
+                        col_idx=col_local, inv_outdeg=inv.contiguous(), outdeg_local=od,
+                        blocks=blocks, block_nnz=block_nnz, hub=hub)
 
 
 class ShardedPageRank:
@@ -122,6 +194,7 @@ class ShardedPageRank:
             self.heap = heap or default_heap(max(1 << 30, 2 * graph.V * 4 + (64 << 20)))
             self.region = self.heap.region(f"pagerank_V{graph.V}", 2 * graph.V * 4, _native.MAX_RANKS)
             self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)
+            self._hub = graph.hub.c_struct() if graph.hub is not None else None
         else:
             self.c = None
         self.reset()
@@ -193,18 +266,31 @@ class ShardedPageRank:
         g, cfg = self.g, self.cfg
         base, damp = cfg.q / self.n, 1.0 - cfg.q
         if self.backend == "fused":
-            _native.check(self.lib.dapb_pagerank_step(
-                self.heap.comm_ref(), g.row_ptr.data_ptr(), g.col_idx.data_ptr(), g.inv_outdeg.data_ptr(),
-                g.blocks.data_ptr(), g.blocks.numel() - 1, self.nv, g.v0, g.V,
-                base, damp, self.ranks_local.data_ptr(), self.region.payload_off, self.region.flag_base,
-                self.region.next_epoch(), self.ticket.data_ptr(), 0 if self._first else 1, int(self.it >= self._skip_from and self.skip_empty), self.grid,
-                _native.stream_ptr()), "pagerank_step")
+            wait_prev, skip = 0 if self._first else 1, int(self.it >= self._skip_from and self.skip_empty)
+            if g.hub is not None:               # warp-granular kernel + hub rows (csrc/pagerank.cu)
+                _native.check(self.lib.dapb_pagerank_step_v2(
+                    self.heap.comm_ref(), g.row_ptr.data_ptr(), g.col_idx.data_ptr(), g.inv_outdeg.data_ptr(),
+                    g.blocks.data_ptr(), g.blocks.numel() - 1, self.nv, g.v0, g.V, C.byref(self._hub),
+                    base, damp, self.ranks_local.data_ptr(), self.region.payload_off, self.region.flag_base,
+                    self.region.next_epoch(), self.ticket.data_ptr(), wait_prev, skip, self.grid,
+                    _native.stream_ptr()), "pagerank_step_v2")
+            else:
+                _native.check(self.lib.dapb_pagerank_step(
+                    self.heap.comm_ref(), g.row_ptr.data_ptr(), g.col_idx.data_ptr(), g.inv_outdeg.data_ptr(),
+                    g.blocks.data_ptr(), g.blocks.numel() - 1, self.nv, g.v0, g.V,
+                    base, damp, self.ranks_local.data_ptr(), self.region.payload_off, self.region.flag_base,
+                    self.region.next_epoch(), self.ticket.data_ptr(), wait_prev, skip, self.grid,
+                    _native.stream_ptr()), "pagerank_step")
             self._first = False
         else:
             vals = self.c[g.col_idx.long()]
             rows = torch.repeat_interleave(torch.arange(self.nv, device=vals.device), g.row_ptr[1:] - g.row_ptr[:-1])
             s = torch.zeros(self.nv, dtype=self.dtype, device=vals.device)
             s.index_add_(0, rows, vals)
+            if g.hub is not None and g.hub.rows.numel():          # long rows live outside the main CSR
+                h = g.hub
+                hrows = torch.repeat_interleave(h.rows.long(), h.ptr[1:] - h.ptr[:-1])
+                s.index_add_(0, hrows, self.c[h.col.long()])
             r = torch.where(s > 0, base + damp * s, torch.zeros_like(s))
             self.ranks_local = r
             self.c = self._gather(r * self.inv)

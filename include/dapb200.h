@@ -201,6 +201,25 @@ DAPB_API int dapb_pagerank_step(const DapbComm* comm, const int64_t* row_ptr, co
                                 uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t skip_empty,
                                 int32_t grid, void* stream);
 
+/* Warp-granular variant: one warp per row block of <= 512 (non-zeros + rows); rows longer than the host's hub
+ * threshold are removed from the main CSR (length 0 there) and described here: their non-zeros live in hub_col, cut
+ * into chunks [chunk_start, chunk_end) that belong to hub rows hub_chunk_ptr[i] .. hub_chunk_ptr[i+1]. */
+typedef struct DapbPrHub {
+  const int32_t* hub_rows;      /* [n_hub] local row ids, ascending */
+  const int32_t* hub_col;       /* non-zeros (source ids) of all hub rows, row after row */
+  const int64_t* chunk_start;   /* [n_chunks] offsets into hub_col */
+  const int64_t* chunk_end;     /* [n_chunks] */
+  const int32_t* hub_chunk_ptr; /* [n_hub + 1] */
+  float* chunk_partial;         /* [n_chunks] scratch */
+  int32_t n_hub, n_chunks;
+} DapbPrHub;
+DAPB_API int dapb_pagerank_step_v2(const DapbComm* comm, const int64_t* row_ptr, const int32_t* col_idx,
+                                   const float* inv_outdeg, const int32_t* blocks, int32_t n_blocks,
+                                   int64_t nv_local, int64_t v0, int64_t V, const DapbPrHub* hub, float base,
+                                   float damp, float* ranks_local, uint64_t c_off, uint32_t flag_base,
+                                   uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t skip_empty,
+                                   int32_t grid, void* stream);
+
 /* ------------------------------------------------------------------ F6 transitive closure --
  * ref: graph_computation/transitive_closure.py:27-40.  Pairs are packed (x << 32 | z); the hash set
  * is open-addressing with 0xFFFF...F as the empty marker (memset 0xFF) and a power-of-two capacity

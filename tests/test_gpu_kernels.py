@@ -256,6 +256,36 @@ def test_pagerank_heavy_row_path(dist):
     np.testing.assert_allclose(outs[0], base.ranks().cpu().numpy(), rtol=1e-4, atol=1e-9)
 
 
+@pytest.mark.parametrize("layout,thr,chunk", [("cta", 0, 0), ("warp", 2048, 2048), ("warp", 16, 64), ("warp", 100000, 2048)])
+def test_pagerank_layouts_skewed_graph(dist, layout, thr, chunk):
+    """Skewed in-degrees: CTA-wide blocks, warp blocks + hub rows (several chunks per hub), and warp blocks whose long
+    rows (> 512 non-zeros, below the hub threshold) take the lane-strided fallback -- all against fp64 torch."""
+    from distributed_algorithm_pyspark_b200.config import PageRankConfig
+    from distributed_algorithm_pyspark_b200.models.pagerank import ShardedPageRank, build_sharded_graph
+    g = torch.Generator(device="cpu").manual_seed(9)
+    V, E = 20000, 400000
+    src = torch.randint(0, V, (E,), generator=g)
+    dst = (torch.randint(0, V, (E,), generator=g).double() ** 3 / V ** 2).long()      # a few very heavy rows
+    src, dst = src.to(DEV), dst.to(DEV)
+    kw = {} if layout == "cta" else dict(hub_threshold=thr, hub_chunk=chunk)
+    gr = build_sharded_graph(src, dst, V, dist, layout=layout, **kw)
+    lens = gr.row_ptr[1:] - gr.row_ptr[:-1]
+    if layout == "warp":
+        assert int(lens.max()) <= thr
+        if thr == 16:
+            assert gr.hub.rows.numel() > 100 and gr.hub.chunk_start.numel() > gr.hub.rows.numel()
+        if thr == 100000:
+            assert gr.hub.rows.numel() == 0 and int(lens.max()) > 512
+    ref_g = build_sharded_graph(src, dst, V, dist, layout="cta")
+    ref = ShardedPageRank(ref_g, PageRankConfig(), dist, backend="nccl", dtype=torch.float64)
+    pr = ShardedPageRank(gr, PageRankConfig(), dist, backend="fused")
+    for _ in range(6):
+        ref.step(); pr.step()
+    a, b = pr.ranks().double(), ref.ranks()
+    assert torch.equal(a > 0, b > 0)
+    assert float(((a - b).abs() / b.clamp(min=1e-30))[b > 0].max()) < 1e-4
+
+
 # ------------------------------------------------------------------------------------------ F6
 def test_transitive_closure_fused_vs_oracle(dist):
     from distributed_algorithm_pyspark_b200.models.transitive_closure import run_transitive_closure
