@@ -1,0 +1,14 @@
+#!/bin/bash
+# One ncu capture per changed hot kernel (each only after the identical plain command exited 0).
+mkdir -p gpurun_out
+run() {  # name regex skip cmd...
+  local name=$1 regex=$2 skip=$3; shift 3
+  "$@" > gpurun_out/ncu_plain_$name.log 2>&1 && \
+  ncu --set full --clock-control none --import-source on -k regex:$regex -s $skip -c 1 -f -o gpurun_out/prof_$name "$@" > gpurun_out/ncu_$name.log 2>&1
+  echo "ncu $name rc=$?"
+}
+run kmeans_tc kmeans_tc_kernel 0 python tests/_tc_worker.py kmeans 8000000 128 1024 0
+run pagerank_warp pagerank_warp_kernel 3 python -m benchmarks.extras --only pagerank --pagerank-scale 24
+run pagerank_hub pagerank_hub_partial_kernel 3 python -m benchmarks.extras --only pagerank --pagerank-scale 24
+run tc_closure tc_closure_kernel 1 python -m benchmarks.extras --only tc
+ls -la gpurun_out/*.ncu-rep
