@@ -41,11 +41,11 @@ struct PrArgs {
   int32_t skip_empty;       // rows without in-edges already hold 0 in BOTH buffers (from the 3rd iteration on)
 };
 
-__device__ __forceinline__ void pr_finish_row(const PrArgs& a, const DapbComm& c, float* c_next_local,
-                                               int64_t row, float s) {
+__device__ __forceinline__ void pr_finish_row_io(const PrArgs& a, const DapbComm& c, float* c_next_local,
+                                                  int64_t row, float s, float inv_outdeg) {
   const float r = s > 0.f ? a.base + a.damp * s : 0.f;          // ref pagerank.py:57 + presence rule
   a.ranks_local[row] = r;
-  const float cn = r * a.inv_outdeg[row];                        // ref pagerank.py:21-25
+  const float cn = r * inv_outdeg;                               // ref pagerank.py:21-25
   const int64_t v = a.v0 + row;
   if (c.world == 1) {
     c_next_local[v] = cn;
@@ -54,6 +54,10 @@ __device__ __forceinline__ void pr_finish_row(const PrArgs& a, const DapbComm& c
     for (int g = 0; g < c.world; ++g)
       reinterpret_cast<float*>(comm_payload(c, g, a.c_off))[((a.epoch & 1) * a.V) + v] = cn;
   }
+}
+__device__ __forceinline__ void pr_finish_row(const PrArgs& a, const DapbComm& c, float* c_next_local,
+                                               int64_t row, float s) {
+  pr_finish_row_io(a, c, c_next_local, row, s, a.inv_outdeg[row]);
 }
 
 // CSR-stream SpMV: a CTA takes a block of consecutive rows holding <= kPrCap non-zeros, gathers ALL their
@@ -171,7 +175,9 @@ __device__ __forceinline__ void pr_wait_prev(const PrArgs& a, const DapbComm& c)
   }
 }
 
-// lane-strided sum of c_cur[col[e]] for e in [b0, b1), 8 gathers in flight per lane; result valid on every lane
+// lane-strided sum of c_cur[col[e]] for e in [b0, b1), up to 8 gathers in flight per lane (predicated in the last
+// batch: a plain remainder loop would keep ONE gather in flight, and most hub rows are shorter than 256);
+// result valid on every lane
 __device__ __forceinline__ float pr_warp_row_sum(const float* __restrict__ c_cur, const int32_t* __restrict__ col,
                                                  int64_t b0, int64_t b1, int lane) {
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
@@ -185,7 +191,15 @@ __device__ __forceinline__ float pr_warp_row_sum(const float* __restrict__ c_cur
     for (int j = 0; j < 8; ++j) f[j] = __ldcg(c_cur + u[j]);
     s0 += f[0] + f[4]; s1 += f[1] + f[5]; s2 += f[2] + f[6]; s3 += f[3] + f[7];
   }
-  for (; e < b1; e += 32) s0 += __ldcg(c_cur + col[e]);
+  if (e < b1) {                                            // warp-uniform tail of fewer than 8 full strides
+    int32_t u[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) u[j] = e + j * 32 < b1 ? col[e + j * 32] : -1;
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = u[j] >= 0 ? __ldcg(c_cur + u[j]) : 0.f;
+    s0 += f[0] + f[4]; s1 += f[1] + f[5]; s2 += f[2] + f[6]; s3 += f[3] + f[7];
+  }
   return warp_sum((s0 + s1) + (s2 + s3));
 }
 
@@ -206,6 +220,11 @@ __global__ void __launch_bounds__(kPrThreads) pagerank_warp_kernel(PrArgs a, Dap
     if (e1 - e0 <= kWarpCap) {
       const int nnz = (int)(e1 - e0);
       const int32_t* ci = a.col_idx + e0;
+      // row extents and 1/outdeg of the first 32 rows are requested BEFORE the gathers so that their latency overlaps
+      int r = r0 + lane;
+      int64_t p0 = 0, p1 = 0;
+      float io = 0.f;
+      if (r < r1) { p0 = a.row_ptr[r]; p1 = a.row_ptr[r + 1]; io = a.inv_outdeg[r]; }
       int32_t u[kWarpCap / 32];
 #pragma unroll
       for (int j = 0; j < kWarpCap / 32; ++j) u[j] = lane + j * 32 < nnz ? ci[lane + j * 32] : -1;
@@ -215,12 +234,18 @@ __global__ void __launch_bounds__(kPrThreads) pagerank_warp_kernel(PrArgs a, Dap
 #pragma unroll
       for (int j = 0; j < kWarpCap / 32; ++j) vals[lane + j * 32] = f[j];
       __syncwarp();
-      for (int r = r0 + lane; r < r1; r += 32) {
-        const int b0 = (int)(a.row_ptr[r] - e0), b1 = (int)(a.row_ptr[r + 1] - e0);
-        if (b1 == b0 && (a.skip_empty || pr_is_hub(h, r))) continue;   // stays 0 / written by the hub kernels
-        float s = 0.f;
-        for (int j = b0; j < b1; ++j) s += vals[j];
-        pr_finish_row(a, c, c_next_local, r, s);
+      while (r < r1) {
+        const int rn = r + 32;                                         // next row of this lane: prefetch its extents
+        int64_t q0 = 0, q1 = 0;
+        float ion = 0.f;
+        if (rn < r1) { q0 = a.row_ptr[rn]; q1 = a.row_ptr[rn + 1]; ion = a.inv_outdeg[rn]; }
+        const int b0 = (int)(p0 - e0), b1 = (int)(p1 - e0);
+        if (!(b1 == b0 && (a.skip_empty || pr_is_hub(h, r)))) {        // else: stays 0 / written by the hub kernels
+          float s = 0.f;
+          for (int j = b0; j < b1; ++j) s += vals[j];
+          pr_finish_row_io(a, c, c_next_local, r, s, io);
+        }
+        r = rn; p0 = q0; p1 = q1; io = ion;
       }
       __syncwarp();
     } else {                                                            // block with a row of 512 .. hub_threshold non-zeros
