@@ -82,6 +82,14 @@ def main():
         pb.step()
     ra, rb = pa.ranks(), pb.ranks()
     out["pagerank_rel_diff"] = float(((ra - rb).abs() / (rb.abs() + 1e-12)).max().item())
+    # ---- transitive closure of a supercritical graph: buffers must grow mid-run on every rank (persistent kernel:
+    #      status GROW decided from the in-kernel message matrix, no host collective), three drivers must agree
+    from distributed_algorithm_pyspark_b200.models.transitive_closure import closure_device
+    rs = np.random.RandomState(11)
+    ts, td = torch.as_tensor(rs.randint(0, 700, 1500), device=dev), torch.as_tensor(rs.randint(0, 700, 1500), device=dev)
+    out["tc"] = [list(closure_device(ts, td, 700, "fused", dist, persistent=True)[:2]),
+                 list(closure_device(ts, td, 700, "fused", dist, persistent=False)[:2]),
+                 list(closure_device(ts, td, 700, "torch", dist)[:2])]
     # ---- Gram with fused all-reduce
     A = torch.randn(5000, 96, device=dev)
     op = GramOp(96, 96, torch.float32, dev, dist, heap=heap, tag="mg")

@@ -70,3 +70,4 @@ def test_engines_fused_vs_nccl_multi_gpu(tmp_path):
     assert out["kmeans_rel_diff"] < 1e-2
     assert out["pagerank_rel_diff"] < 1e-3
     assert out["gram_rel_diff"] < 1e-4
+    assert out["tc"] == [[337025, 18]] * 3, out["tc"]          # oracle: 337025 pairs after 18 rounds
