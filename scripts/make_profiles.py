@@ -80,7 +80,9 @@ def sass_listings():
     wanted = {"kmeans_tc_kernelILi128": "kmeans_tc_kernel_d128", "gram_tc_kernel": "gram_tc_kernel",
               "lr_step_kernelI13__nv_bfloat16Li32": "lr_step_kernel_bf16_d1024", "lr_parity_kernel": "lr_parity_kernel",
               "pagerank_step_kernel": "pagerank_step_kernel", "mc_pi_kernel": "mc_pi_kernel", "tc_expand_kernel": "tc_expand_kernel",
-              "kmeans_finalize_kernelIfE": "kmeans_finalize_kernel_f32", "lr_tc_kernel": "lr_tc_kernel"}
+              "kmeans_finalize_kernelIfE": "kmeans_finalize_kernel_f32", "lr_tc_kernel": "lr_tc_kernel",
+              "pagerank_warp_kernel": "pagerank_warp_kernel", "pagerank_hub_partial_kernel": "pagerank_hub_partial_kernel",
+              "tc_closure_kernel": "tc_closure_kernel"}
     summary = ["# SASS evidence per hot kernel", "",
                "`cuobjdump -sass` of `distributed_algorithm_pyspark_b200/_lib/libdapb200.so` (sm_100a).  `UTCHMMA` = tcgen05.mma, "
                "`LDTM` = tcgen05.ld, `UTMALDG` = TMA tensor load, `UTCBAR` = tcgen05.commit, `SYNCS` = mbarrier ops, "
