@@ -72,7 +72,7 @@ struct SmemLayout {
 struct KmTcArgs {
   const __nv_bfloat16* X; // [n, KD]
   int64_t n;              // rows
-  int k;                  // centroids (multiple of 128, <= 1024)
+  int k;                  // centroids incl. padding (multiple of 128, <= 16384)
   const float* cnorm;     // [k]
   float* sums;            // [k, KD]
   int* counts;            // [k]
@@ -432,11 +432,15 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 // centres fp32 [k, d] -> tensor-core operand bf16(-2 c) [k, d] and ||bf16(c)||^2 (the norm of the ROUNDED centre,
 // so that the assignment is the exact nearest neighbour w.r.t. one consistent set of centres); cnorm[k] receives
 // max_j ||c_j||^2 (as float bits; norms are >= 0 so the integer order is the float order)
-__global__ void kmeans_tc_prep_kernel(const float* __restrict__ C, int k, int d, __nv_bfloat16* __restrict__ Bp,
+__global__ void kmeans_tc_prep_kernel(const float* __restrict__ C, int k, int k_pad, int d, __nv_bfloat16* __restrict__ Bp,
                                       float* __restrict__ cnorm) {
   const int lane = threadIdx.x & 31;
   const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (c >= k) return;
+  if (c >= k_pad) return;
+  if (c >= k) {                                   // padding centroid: zero operand row, norm set by the bias kernel
+    for (int j = lane; j < d; j += 32) Bp[(size_t)c * d + j] = __float2bfloat16(0.f);
+    return;
+  }
   float s = 0.f;
   for (int j = lane; j < d; j += 32) {
     const __nv_bfloat16 cb = __float2bfloat16(C[(size_t)c * d + j]);
@@ -447,22 +451,25 @@ __global__ void kmeans_tc_prep_kernel(const float* __restrict__ C, int k, int d,
   s = warp_sum(s);
   if (lane == 0) {
     cnorm[c] = s;
-    atomicMax(reinterpret_cast<int*>(cnorm + k), __float_as_int(s));
+    atomicMax(reinterpret_cast<int*>(cnorm + k_pad), __float_as_int(s));
   }
 }
 
-// cnorm[j] += C1 with C1 = 1.5 * 2^E, 2^(E-1) > M >= |x.x - ||x||^2 - 2 x.c + ...| = |cn_j - 2 x.c_j| for every row x
-// and centre j: M = cn_max + 2 sqrt(xn_max * cn_max) (Cauchy-Schwarz) with 1 % slack for the fp32 accumulation.
+// cnorm[j] += C1 with C1 = 1.5 * 2^E, 2^(E-1) > M >= |cn_j - 2 x.c_j| for every row x and centre j:
+// M = cn_max + 2 sqrt(xn_max * cn_max) (Cauchy-Schwarz) with 1 % slack for the fp32 accumulation.
 // Then C1 + (cn_j - 2 x.c_j) lies in [2^E, 2^(E+1)): one common exponent, resolution 2^(E-23) <= M * 2^-20.
-__global__ void kmeans_tc_bias_kernel(float* __restrict__ cnorm, int k, float xnorm_max) {
-  const float cmax = cnorm[k];
+// Padding centroids (k .. k_pad) get C1 + 0.9999 * 2^(E-1): inside the binade and above every real distance
+// (those stay below M / 1.01), so they never win.
+__global__ void kmeans_tc_bias_kernel(float* __restrict__ cnorm, int k, int k_pad, float xnorm_max) {
+  const float cmax = cnorm[k_pad];
   const float M = 1.01f * (cmax + 2.0f * sqrtf(xnorm_max * cmax)) + 1e-30f;
   int e;
   frexpf(M, &e);                                  // M = f * 2^e, f in [0.5, 1)  =>  M < 2^e
   const float C1 = ldexpf(1.5f, e + 1);           // E = e + 1: 2^(E-1) = 2^e > M
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j < k) cnorm[j] += C1;
-  if (j == 0) cnorm[k + 1] = C1;
+  else if (j < k_pad) cnorm[j] = C1 + ldexpf(0.9999f, e);
+  if (j == 0) cnorm[k_pad + 1] = C1;
 }
 
 template <int KD>
@@ -478,17 +485,19 @@ int launch_km(const CUtensorMap& mx, const CUtensorMap& mc, KmTcArgs a, int grid
 
 }  // namespace
 
-// cnorm: [k + 8] floats (k biased norms, then the running max and the bias, see above); xnorm_max >= max_i ||x_i||^2
-// over every row the assignment kernel will see (a looser bound only costs resolution).
+// k_pad = k rounded up to a multiple of 128 (the MMA's N); b_operand: [k_pad, d] bf16; cnorm: [k_pad + 8] floats
+// (k_pad biased norms, then the running max and the bias, see above); xnorm_max >= max_i ||x_i||^2 over every row the
+// assignment kernel will see (a looser bound only costs resolution).
 extern "C" int dapb_kmeans_tc_prepare(const float* centers, int32_t k, int32_t d, void* b_operand, float* cnorm,
                                       float xnorm_max, void* stream) {
   DAPB_REQUIRE(centers && b_operand && cnorm && k >= 1 && d >= 1, "kmeans_tc_prepare: bad arguments");
   DAPB_REQUIRE(xnorm_max >= 0.f && xnorm_max < 1e30f, "kmeans_tc_prepare: xnorm_max must be a finite bound on ||x||^2");
-  DAPB_CUDA_CHECK(cudaMemsetAsync(cnorm + k, 0, 8 * sizeof(float), (cudaStream_t)stream));
-  const int blocks = (k * 32 + 255) / 256;
-  kmeans_tc_prep_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(centers, k, d, (__nv_bfloat16*)b_operand, cnorm);
+  const int k_pad = (k + kNB - 1) / kNB * kNB;
+  DAPB_CUDA_CHECK(cudaMemsetAsync(cnorm + k_pad, 0, 8 * sizeof(float), (cudaStream_t)stream));
+  const int blocks = (k_pad * 32 + 255) / 256;
+  kmeans_tc_prep_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(centers, k, k_pad, d, (__nv_bfloat16*)b_operand, cnorm);
   DAPB_LAUNCH_CHECK();
-  kmeans_tc_bias_kernel<<<(k + 255) / 256, 256, 0, (cudaStream_t)stream>>>(cnorm, k, xnorm_max);
+  kmeans_tc_bias_kernel<<<(k_pad + 255) / 256, 256, 0, (cudaStream_t)stream>>>(cnorm, k, k_pad, xnorm_max);
   DAPB_LAUNCH_CHECK();
   return 0;
 }
@@ -509,7 +518,8 @@ extern "C" int dapb_kmeans_assign_tc_dbg(const void* X, int64_t n, int32_t d, co
                                          int32_t* counts, int32_t grid, long long* dbg, void* stream) {
   DAPB_REQUIRE(X && b_operand && cnorm && sums && counts, "kmeans_assign_tc: null argument");
   DAPB_REQUIRE(d == 64 || d == 128, "kmeans_assign_tc: d must be 64 or 128 (got %d)", d);
-  DAPB_REQUIRE(k >= 128 && k <= 1024 && k % 128 == 0, "kmeans_assign_tc: k must be a multiple of 128 in [128, 1024] (got %d)", k);
+  DAPB_REQUIRE(k >= 1 && k <= 16384, "kmeans_assign_tc: k must be in [1, 16384] (got %d)", k);
+  k = (k + kNB - 1) / kNB * kNB;                  // padding centroids of dapb_kmeans_tc_prepare never win
   DAPB_REQUIRE(n >= 1 && n < (1ll << 31) - 256, "kmeans_assign_tc: n out of range for 32-bit TMA coordinates");
   CUtensorMap mx, mc;
   int rc = make_tensor_map_bf16_2d(&mx, X, (uint64_t)n, (uint64_t)d, (uint64_t)d, 64, kTM);

@@ -7,11 +7,11 @@ from .. import _native
 
 
 def supported(X: torch.Tensor, k: int) -> bool:
-    """bf16 points with d in {64, 128}, k a multiple of 128 up to 1024, at least one full tile of rows."""
+    """bf16 points with d in {64, 128}, 1 <= k <= 16384 (padded to a multiple of 128 inside), at least one full tile of rows."""
     lib = _native.load()
     if not hasattr(lib, "dapb_kmeans_assign_tc"):
         return False
-    return (X.is_cuda and X.dtype == torch.bfloat16 and X.shape[1] in (64, 128) and k % 128 == 0 and 128 <= k <= 1024
+    return (X.is_cuda and X.dtype == torch.bfloat16 and X.shape[1] in (64, 128) and 1 <= k <= 16384
             and X.shape[0] >= 128 and X.data_ptr() % 16 == 0)
 
 
@@ -23,8 +23,9 @@ class KMeansTC:
         self.X, self.k = X, int(k)
         self.n, self.d = X.shape
         self.grid = grid
-        self.b_operand = torch.empty(self.k, self.d, dtype=torch.bfloat16, device=X.device)
-        self.cnorm = torch.empty(self.k + 8, dtype=torch.float32, device=X.device)
+        k_pad = (self.k + 127) // 128 * 128                     # the MMA's N granularity; padding centroids never win
+        self.b_operand = torch.empty(k_pad, self.d, dtype=torch.bfloat16, device=X.device)
+        self.cnorm = torch.empty(k_pad + 8, dtype=torch.float32, device=X.device)
         # max ||x||^2 over the resident shard (X never changes): bounds every distance, so the kernel can compare
         # fixed-exponent bit patterns instead of floats.  One chunked pass at construction.
         xmax = 0.0

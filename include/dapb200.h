@@ -174,9 +174,10 @@ DAPB_API int dapb_kmeans_finalize(const DapbComm* comm, void* sums, int32_t* cou
                                   int32_t d, int32_t f64, uint64_t payload_off, uint32_t flag_base,
                                   uint64_t epoch, int32_t* counts_out, int32_t clear_partials, void* stream);
 DAPB_API uint64_t dapb_kmeans_payload_bytes(int32_t world, int32_t k, int32_t d, int32_t elem_bytes);
-/* Tensor-core assignment (tcgen05.mma + TMEM + TMA), bf16 points, d in {64,128}, k multiple of 128 <= 1024.
+/* Tensor-core assignment (tcgen05.mma + TMEM + TMA), bf16 points, d in {64,128}, 1 <= k <= 16384; b_operand and cnorm
+ * are sized for k_pad = k rounded up to a multiple of 128 ([k_pad, d] bf16 and k_pad + 8 floats).
  * dapb_kmeans_tc_prepare turns fp32 centres into the bf16 operand (-2c) [k,d] and the BIASED norms
- * ||bf16(c)||^2 + C1 in cnorm[0..k) (cnorm holds k + 8 floats; C1 makes all distances share one exponent so that the
+ * ||bf16(c)||^2 + C1 in cnorm[0..k) (C1 makes all distances share one exponent so that the
  * arg-min runs on integer keys, see csrc/kmeans_tc.cu).  xnorm_max: an upper bound on ||x||^2 over all rows. */
 DAPB_API int dapb_kmeans_tc_prepare(const float* centers, int32_t k, int32_t d, void* b_operand, float* cnorm,
                                     float xnorm_max, void* stream);

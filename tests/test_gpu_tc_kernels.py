@@ -26,6 +26,9 @@ def run_case(*args, timeout=180):
     (128 * 4 * 7 + 77, 128, 256, 2),     # several super tiles per CTA (slot / stage / TMEM ring wrap-around) + ragged tail
     (128 * 37 + 5, 64, 384, 3),          # d = 64, k not a power of two
     (200000, 128, 1024, 0),              # benchmark-shaped k, full grid
+    (3000, 128, 100, 2),                 # k below one chunk: 28 padding centroids that must never win
+    (5000, 64, 1000, 0),                 # k not a multiple of 128
+    (20000, 128, 2048, 0),               # 16 chunks
 ])
 def test_kmeans_tc_assignment_and_sums(n, d, k, grid):
     r = run_case("kmeans", n, d, k, grid)
