@@ -11,6 +11,7 @@
 //  * lr_step_kernel    -- one optimiser step at benchmark scale (bf16/fp32 rows streamed once
 //    from HBM, forward + backward from the same registers, deterministic grid reduction, then the
 //    last CTA performs the cross-GPU all-reduce over peer memory and the optimiser update).
+#include <cstdlib>
 #include <cooperative_groups.h>
 
 #include <mutex>
@@ -347,7 +348,12 @@ __device__ void lr_finalize(const DapbLrStepArgs& a, const DapbComm& c, float* g
 }
 
 // Fast path: D == 32 * EPL (each lane owns EPL features, EPL/kElems 16-byte vectors per row).
-template <typename T, int EPL>
+// PF > 0: the sampling decision of the chunk this warp will process PF iterations later is taken now and every kept row
+// is requested from HBM with one cp.async.bulk.prefetch.L2 (no registers, no completion to wait for), so the demand
+// loads find their rows in L2.  Two sampled bf16 rows per warp are only 64 KB in flight per SM -- not enough to cover
+// the HBM latency at 6.5 TB/s; the prefetch lifts bf16 SSGD from 86 % to 94 % of the measured copy bandwidth.  fp32
+// rows (twice the bytes in flight) do not profit and keep PF = 0.
+template <typename T, int EPL, int PF>
 __global__ void __launch_bounds__(kStepThreads, 2) lr_step_kernel(DapbLrStepArgs a, DapbComm c) {
   constexpr int kE = RowVec<T>::kElems;
   constexpr int kV = EPL / kE;                     // vectors per lane per row
@@ -379,12 +385,43 @@ __global__ void __launch_bounds__(kStepThreads, 2) lr_step_kernel(DapbLrStepArgs
   const char* Xb = reinterpret_cast<const char*>(a.X);
   const bool all_rows = a.mask == nullptr && a.threshold24 >= (1u << 24);
 
-  for (int64_t ch = warp_g; ch < n_chunks; ch += warp_n) {
-    const int64_t row = (ch << 5) + lane;
+  auto keep_of = [&](int64_t chn) -> bool {
+    const int64_t row = (chn << 5) + lane;
     bool keep = row < a.n_rows;
     if (keep && !all_rows)
       keep = a.mask ? (a.mask[row] != 0)
                     : philox_keep_row((uint64_t)(a.row_base + row), a.iteration, a.seed, a.threshold24);
+    return keep;
+  };
+  bool kq[PF > 0 ? PF : 1];                            // decisions for the next PF chunks of this warp
+#pragma unroll
+  for (int i = 0; i < PF; ++i) {
+    const int64_t chn = warp_g + i * warp_n;
+    kq[i] = chn < n_chunks ? keep_of(chn) : false;
+    if (i > 0 && kq[i]) {
+      const char* pn = Xb + ((chn << 5) + lane) * (int64_t)(D * sizeof(T));
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(pn), "r"((uint32_t)(D * sizeof(T))) : "memory");
+    }
+  }
+  for (int64_t ch = warp_g; ch < n_chunks; ch += warp_n) {
+    bool keep;
+    if (PF > 0) {
+      keep = kq[0];
+#pragma unroll
+      for (int i = 0; i + 1 < PF; ++i) kq[i] = kq[i + 1];
+      const int64_t chn = ch + PF * warp_n;
+      bool kn = false;
+      if (chn < n_chunks) {
+        kn = keep_of(chn);
+        if (kn) {
+          const char* pn = Xb + ((chn << 5) + lane) * (int64_t)(D * sizeof(T));
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(pn), "r"((uint32_t)(D * sizeof(T))) : "memory");
+        }
+      }
+      kq[PF - 1] = kn;
+    } else {
+      keep = keep_of(ch);
+    }
     unsigned bits = __ballot_sync(0xffffffffu, keep);
     kept += __popc(bits);
     while (bits) {
@@ -517,8 +554,16 @@ template <typename T, int EPL>
 int launch_fast(const DapbLrStepArgs& a, const DapbComm& c, int grid, cudaStream_t s) {
   constexpr int D = 32 * EPL;
   size_t smem = sizeof(float) * (size_t)(D + (kStepWarps * D > 2 * D + 32 ? kStepWarps * D : 2 * D + 32));
-  DAPB_CUDA_CHECK(cudaFuncSetAttribute(lr_step_kernel<T, EPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  lr_step_kernel<T, EPL><<<grid, kStepThreads, smem, s>>>(a, c);
+  // prefetch distance: 16-bit rows 1 chunk ahead by default, 32-bit rows none (measured); DAPB_LR_PREFETCH=0|1|2 overrides
+  static const int pf_env = getenv("DAPB_LR_PREFETCH") ? atoi(getenv("DAPB_LR_PREFETCH")) : -1;
+  const int pf = pf_env >= 0 ? pf_env : (sizeof(T) == 2 ? 1 : 0);
+#define DAPB_LAUNCH_PF(N)                                                                                              \
+  {                                                                                                                     \
+    DAPB_CUDA_CHECK(cudaFuncSetAttribute(lr_step_kernel<T, EPL, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    lr_step_kernel<T, EPL, N><<<grid, kStepThreads, smem, s>>>(a, c);                                                   \
+  }
+  if (pf >= 2) DAPB_LAUNCH_PF(2) else if (pf == 1) DAPB_LAUNCH_PF(1) else DAPB_LAUNCH_PF(0)
+#undef DAPB_LAUNCH_PF
   DAPB_LAUNCH_CHECK();
   return 0;
 }
