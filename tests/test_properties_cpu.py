@@ -64,3 +64,33 @@ def test_philox_mask_is_offset_consistent(n, seed, it):
     full = philox_row_mask_np(n, 0.3, seed, it, 0)
     cut = n // 3
     assert (philox_row_mask_np(n - cut, 0.3, seed, it, cut) == full[cut:]).all()
+
+
+@given(st.lists(st.integers(0, 40), min_size=1, max_size=60), st.integers(0, 30), st.integers(1, 17))
+@settings(max_examples=60, deadline=None, suppress_health_check=list(HealthCheck))
+def test_hub_split_is_a_lossless_rearrangement(lens, threshold, chunk):
+    """split_hub_rows (PageRank warp layout): main CSR + hub rows/chunks together hold every non-zero exactly once, in
+    row order, and the chunks tile each hub row without gaps."""
+    import torch
+    from distributed_algorithm_pyspark_b200.models.pagerank import split_hub_rows
+    lens_t = torch.tensor(lens, dtype=torch.int64)
+    row_ptr = torch.zeros(len(lens) + 1, dtype=torch.int64)
+    row_ptr[1:] = torch.cumsum(lens_t, 0)
+    col = torch.arange(int(row_ptr[-1]), dtype=torch.int32)            # non-zero e carries the id e
+    rp, main_col, hub = split_hub_rows(row_ptr, col, threshold, chunk)
+    hub_rows = set(hub.rows.tolist())
+    assert hub_rows == {i for i, l in enumerate(lens) if l > threshold}
+    rebuilt = {}
+    for r in range(len(lens)):
+        if r in hub_rows:
+            assert int(rp[r + 1] - rp[r]) == 0
+        else:
+            rebuilt[r] = main_col[int(rp[r]):int(rp[r + 1])].tolist()
+    for i, r in enumerate(hub.rows.tolist()):
+        a, b = int(hub.chunk_ptr[i]), int(hub.chunk_ptr[i + 1])
+        assert b > a and int(hub.chunk_start[a]) == int(hub.ptr[i]) and int(hub.chunk_end[b - 1]) == int(hub.ptr[i + 1])
+        assert all(int(hub.chunk_end[c]) == int(hub.chunk_start[c + 1]) for c in range(a, b - 1))
+        assert all(0 < int(hub.chunk_end[c] - hub.chunk_start[c]) <= chunk for c in range(a, b))
+        rebuilt[r] = hub.col[int(hub.ptr[i]):int(hub.ptr[i + 1])].tolist()
+    for r in range(len(lens)):
+        assert rebuilt[r] == list(range(int(row_ptr[r]), int(row_ptr[r + 1])))
