@@ -175,30 +175,31 @@ __device__ __forceinline__ void pr_wait_prev(const PrArgs& a, const DapbComm& c)
   }
 }
 
-// lane-strided sum of c_cur[col[e]] for e in [b0, b1), up to 8 gathers in flight per lane (predicated in the last
+// lane-strided sum of c_cur[col[e]] for e in [b0, b1), up to kDeep gathers in flight per lane (predicated in the last
 // batch: a plain remainder loop would keep ONE gather in flight, and most hub rows are shorter than 256);
 // result valid on every lane
+template <int kDeep>   // gathers in flight per lane
 __device__ __forceinline__ float pr_warp_row_sum(const float* __restrict__ c_cur, const int32_t* __restrict__ col,
                                                  int64_t b0, int64_t b1, int lane) {
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
   int64_t e = b0 + lane;
-  for (; e + 7 * 32 < b1; e += 8 * 32) {
-    int32_t u[8];
+  for (; e + (kDeep - 1) * 32 < b1; e += kDeep * 32) {
+    int32_t u[kDeep];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) u[j] = col[e + j * 32];
-    float f[8];
+    for (int j = 0; j < kDeep; ++j) u[j] = col[e + j * 32];
+    float f[kDeep];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) f[j] = __ldcg(c_cur + u[j]);
-    s0 += f[0] + f[4]; s1 += f[1] + f[5]; s2 += f[2] + f[6]; s3 += f[3] + f[7];
+    for (int j = 0; j < kDeep; ++j) f[j] = __ldcg(c_cur + u[j]);
+    _Pragma("unroll") for (int j = 0; j < kDeep; j += 4) { s0 += f[j]; s1 += f[j + 1]; s2 += f[j + 2]; s3 += f[j + 3]; }
   }
   if (e < b1) {                                            // warp-uniform tail of fewer than 8 full strides
-    int32_t u[8];
+    int32_t u[kDeep];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) u[j] = e + j * 32 < b1 ? col[e + j * 32] : -1;
-    float f[8];
+    for (int j = 0; j < kDeep; ++j) u[j] = e + j * 32 < b1 ? col[e + j * 32] : -1;
+    float f[kDeep];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) f[j] = u[j] >= 0 ? __ldcg(c_cur + u[j]) : 0.f;
-    s0 += f[0] + f[4]; s1 += f[1] + f[5]; s2 += f[2] + f[6]; s3 += f[3] + f[7];
+    for (int j = 0; j < kDeep; ++j) f[j] = u[j] >= 0 ? __ldcg(c_cur + u[j]) : 0.f;
+    _Pragma("unroll") for (int j = 0; j < kDeep; j += 4) { s0 += f[j]; s1 += f[j + 1]; s2 += f[j + 2]; s3 += f[j + 3]; }
   }
   return warp_sum((s0 + s1) + (s2 + s3));
 }
@@ -252,7 +253,7 @@ __global__ void __launch_bounds__(kPrThreads) pagerank_warp_kernel(PrArgs a, Dap
       for (int r = r0; r < r1; ++r) {
         const int64_t b0 = a.row_ptr[r], b1 = a.row_ptr[r + 1];
         if (b1 == b0 && (a.skip_empty || pr_is_hub(h, r))) continue;
-        const float s = pr_warp_row_sum(c_cur, a.col_idx, b0, b1, lane);
+        const float s = pr_warp_row_sum<8>(c_cur, a.col_idx, b0, b1, lane);
         if (lane == 0) pr_finish_row(a, c, c_next_local, r, s);
       }
     }
@@ -273,13 +274,14 @@ __global__ void __launch_bounds__(kPrThreads) pagerank_warp_kernel(PrArgs a, Dap
   if (tid < c.world) st_release_sys(comm_flags(c, tid) + a.flag_base + c.rank, a.epoch);
 }
 
+constexpr int kHubDeep = 16;     // measured: 8 -> 16 gathers in flight per lane +5..8 %, 32 no better
 __global__ void __launch_bounds__(kPrThreads) pagerank_hub_partial_kernel(PrArgs a, DapbPrHub h, DapbComm c) {
   const int lane = threadIdx.x & 31;
   const float* c_cur = reinterpret_cast<const float*>(comm_payload(c, c.rank, a.c_off)) + (((a.epoch - 1) & 1) * a.V);
   pr_wait_prev(a, c);
   const int n_warps = gridDim.x * kWarpsPerCta;
   for (int ch = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5); ch < h.n_chunks; ch += n_warps) {
-    const float s = pr_warp_row_sum(c_cur, h.hub_col, h.chunk_start[ch], h.chunk_end[ch], lane);
+    const float s = pr_warp_row_sum<kHubDeep>(c_cur, h.hub_col, h.chunk_start[ch], h.chunk_end[ch], lane);
     if (lane == 0) h.chunk_partial[ch] = s;
   }
 }
