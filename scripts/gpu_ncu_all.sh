@@ -13,7 +13,7 @@ run lr_step lr_step_kernel 2 python bench.py --steps 3 --warmup 1 --no-extras --
 run lr_tc lr_tc_kernel 2 python bench.py --steps 3 --warmup 1 --no-extras --no-e2e --rows-per-gpu 8388608 --lr-kernel tc
 run pagerank_warp pagerank_warp_kernel 3 python -m benchmarks.extras --only pagerank --pagerank-scale 24
 run pagerank_hub pagerank_hub_partial_kernel 3 python -m benchmarks.extras --only pagerank --pagerank-scale 24
-run pagerank env DAPB_PR_LAYOUT=cta python -m benchmarks.extras --only pagerank --pagerank-scale 22
+run pagerank pagerank_step_kernel 3 env DAPB_PR_LAYOUT=cta python -m benchmarks.extras --only pagerank --pagerank-scale 22
 run tc_closure tc_closure_kernel 1 python -m benchmarks.extras --only tc
 run mc_pi mc_pi_kernel 0 python -m benchmarks.extras --only mc
 ls -la gpurun_out/*.ncu-rep
