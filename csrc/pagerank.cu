@@ -15,6 +15,7 @@
 // Sharding: rank g owns destination vertices [v0, v1) and the CSR rows of A^T for them; the
 // contribution vector c (all V entries) is replicated in the symmetric heap, double-buffered on the
 // iteration parity: iteration t reads buffer t&1 and pushes into buffer (t+1)&1 of every rank.
+#include <cstdlib>
 #include "comm.cuh"
 
 using namespace dapb;
@@ -39,6 +40,7 @@ struct PrArgs {
   uint32_t* ticket;
   int32_t wait_prev;        // wait for epoch-1 from every rank before reading
   int32_t skip_empty;       // rows without in-edges already hold 0 in BOTH buffers (from the 3rd iteration on)
+  int32_t no_push;          // DAPB_PR_NOPUSH=1: keep contributions local (TIMING EXPERIMENTS ONLY, results are wrong)
 };
 
 __device__ __forceinline__ void pr_finish_row_io(const PrArgs& a, const DapbComm& c, float* c_next_local,
@@ -47,7 +49,7 @@ __device__ __forceinline__ void pr_finish_row_io(const PrArgs& a, const DapbComm
   a.ranks_local[row] = r;
   const float cn = r * inv_outdeg;                               // ref pagerank.py:21-25
   const int64_t v = a.v0 + row;
-  if (c.world == 1) {
+  if (c.world == 1 || a.no_push) {
     c_next_local[v] = cn;
   } else {
 #pragma unroll 1
@@ -335,6 +337,7 @@ extern "C" int dapb_pagerank_step(const DapbComm* comm, const int64_t* row_ptr, 
   a.row_ptr = row_ptr; a.col_idx = col_idx; a.inv_outdeg = inv_outdeg; a.blocks = blocks; a.n_blocks = n_blocks;
   a.nv_local = nv_local; a.v0 = v0; a.V = V; a.base = base; a.damp = damp; a.ranks_local = ranks_local;
   a.c_off = c_off; a.flag_base = flag_base; a.epoch = epoch; a.ticket = ticket; a.wait_prev = wait_prev; a.skip_empty = skip_empty;
+  { static const int np = getenv("DAPB_PR_NOPUSH") ? atoi(getenv("DAPB_PR_NOPUSH")) : 0; a.no_push = np; }
   if (grid <= 0) grid = dapb::sm_count() * 8;
   if (grid > n_blocks) grid = n_blocks > 0 ? n_blocks : 1;
   pagerank_step_kernel<<<grid, kPrThreads, 0, (cudaStream_t)stream>>>(a, *comm);
@@ -360,6 +363,7 @@ extern "C" int dapb_pagerank_step_v2(const DapbComm* comm, const int64_t* row_pt
   a.row_ptr = row_ptr; a.col_idx = col_idx; a.inv_outdeg = inv_outdeg; a.blocks = blocks; a.n_blocks = n_blocks;
   a.nv_local = nv_local; a.v0 = v0; a.V = V; a.base = base; a.damp = damp; a.ranks_local = ranks_local;
   a.c_off = c_off; a.flag_base = flag_base; a.epoch = epoch; a.ticket = ticket; a.wait_prev = wait_prev; a.skip_empty = skip_empty;
+  { static const int np = getenv("DAPB_PR_NOPUSH") ? atoi(getenv("DAPB_PR_NOPUSH")) : 0; a.no_push = np; }
   const DapbPrHub h = *hub;
   cudaStream_t st = (cudaStream_t)stream;
   const int cap = dapb::sm_count() * 8;

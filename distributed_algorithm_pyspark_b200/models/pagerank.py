@@ -102,15 +102,23 @@ def split_hub_rows(row_ptr: torch.Tensor, col_idx: torch.Tensor, threshold: int,
     return rp, main_col, hub
 
 
-def balanced_vertex_bounds(indeg_all: torch.Tensor, world: int, vertex_cost: int = 8):
-    """Contiguous destination-vertex ranges with (almost) equal numbers of in-edges AND vertices per rank: the cost of
-    a vertex is in-degree + 1 (+ vertex_cost if it has in-edges: its new contribution is pushed to every peer each
-    iteration).  R-MAT graphs concentrate edges on low vertex ids, so equal-size ranges would give
-    rank 0 most of the work."""
+def balanced_vertex_bounds(indeg_all: torch.Tensor, world: int, vertex_cost: Optional[float] = None,
+                           hub_threshold: int = 64, hub_edge_cost: Optional[float] = None):
+    """Contiguous destination-vertex ranges of (almost) equal modelled cost per rank.  A vertex costs 1, plus
+    ``vertex_cost`` if it has in-edges (row bookkeeping + its new contribution is pushed to every peer each iteration),
+    plus 1 per in-edge -- ``hub_edge_cost`` per in-edge for hub rows (> hub_threshold in-edges), whose non-zeros are
+    streamed by the cheaper chunk kernel.  R-MAT graphs concentrate edges on low vertex ids, so equal-size ranges would
+    give rank 0 most of the work.  ``DAPB_PR_VERTEX_COST`` / ``DAPB_PR_HUB_EDGE_COST`` override."""
+    if vertex_cost is None:
+        vertex_cost = float(os.environ.get("DAPB_PR_VERTEX_COST", 8))
+    if hub_edge_cost is None:
+        hub_edge_cost = float(os.environ.get("DAPB_PR_HUB_EDGE_COST", 1.0))
     V = indeg_all.numel()
-    cost = torch.cumsum(indeg_all + vertex_cost * (indeg_all > 0) + 1, 0)
-    total = int(cost[-1].item())
-    targets = torch.tensor([(total * r) // world for r in range(1, world)], device=indeg_all.device, dtype=cost.dtype)
+    deg = indeg_all.to(torch.float64)
+    edge = torch.where(indeg_all > hub_threshold, deg * hub_edge_cost, deg)
+    cost = torch.cumsum(edge + vertex_cost * (indeg_all > 0) + 1, 0)
+    total = float(cost[-1].item())
+    targets = torch.tensor([total * r / world for r in range(1, world)], device=indeg_all.device, dtype=cost.dtype)
     cuts = torch.searchsorted(cost, targets, right=False).tolist() if world > 1 else []
     b = [0] + [min(int(c) + 1, V) for c in cuts] + [V]
     for i in range(1, len(b)):
@@ -139,7 +147,8 @@ def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Opti
     outdeg = torch.bincount(s_all, minlength=V)
     n_sources = int((outdeg > 0).sum().item())
     if balance and dist.world > 1:
-        bounds = balanced_vertex_bounds(torch.bincount(d_all, minlength=V), dist.world)
+        bounds = balanced_vertex_bounds(torch.bincount(d_all, minlength=V), dist.world,
+                                        hub_threshold=hub_threshold if layout == "warp" else (1 << 62))
     else:
         bounds = tuple(vertex_range(V, r, dist.world)[0] for r in range(dist.world)) + (V,)
     v0, v1 = bounds[dist.rank], bounds[dist.rank + 1]
