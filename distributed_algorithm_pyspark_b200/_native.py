@@ -7,7 +7,6 @@ The library is loaded lazily.  On a machine with a GPU a missing or unloadable l
 from __future__ import annotations
 
 import ctypes as C
-import os
 from typing import Optional
 
 from . import build as _build

@@ -4,7 +4,7 @@ entry scripts can expose them unchanged.
 """
 from __future__ import annotations
 
-from dataclasses import dataclass, field, asdict
+from dataclasses import dataclass, asdict
 from typing import Optional
 
 

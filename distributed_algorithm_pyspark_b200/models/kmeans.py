@@ -11,7 +11,6 @@ fuses reduce-scatter, mean update and centroid all-gather over NVLink peer memor
 """
 from __future__ import annotations
 
-import ctypes as C
 import os
 from typing import Optional
 

@@ -15,8 +15,7 @@ Three interchangeable backends produce a :class:`LogisticResult`:
 from __future__ import annotations
 
 import ctypes as C
-from dataclasses import dataclass
-from typing import List, Optional
+from typing import Optional
 
 import numpy as np
 import torch

@@ -17,10 +17,9 @@ Backends: ``oracle`` (NumPy, per-row solves as the reference), ``torch`` (matmul
 """
 from __future__ import annotations
 
-import ctypes as C
 import os
 from dataclasses import dataclass
-from typing import List, Optional, Tuple
+from typing import List, Optional
 
 import numpy as np
 import torch

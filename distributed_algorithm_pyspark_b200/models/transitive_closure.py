@@ -11,7 +11,6 @@ Backends: ``oracle`` (Python sets), ``torch`` (sort/unique based, ``all_to_all``
 """
 from __future__ import annotations
 
-import ctypes as C
 import os
 from dataclasses import dataclass
 from typing import Iterable, Optional, Tuple

@@ -6,9 +6,6 @@ keep those names and defaults and add optional flags on top.
 from __future__ import annotations
 
 import argparse
-import contextlib
-import io
-import os
 import sys
 
 

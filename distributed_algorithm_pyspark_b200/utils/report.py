@@ -10,7 +10,7 @@ from __future__ import annotations
 import json
 import os
 import random
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, Sequence
 
 import numpy as np
 
