@@ -45,6 +45,28 @@ def main():
     out["tc"] = {"n": tc.n_pairs, "rounds": tc.rounds, "pairs": tc.pairs.tolist()}
     als = run_als(ALSConfig(m=40, n=60, k=5, seed=0, n_iterations=3), backend=backend, dist=dist)
     out["als"] = {"rmse": als.rmse, "U": als.U.tolist()}
+    # ---- checkpoint / resume under torchrun: stop after a few iterations, resume to the end, compare with the
+    #      uninterrupted results above (PageRank writes one file per rank, the others write on rank 0)
+    ck_dir = out_path + ".ckpt"
+    os.makedirs(ck_dir, exist_ok=True)
+    run_pagerank(e, PageRankConfig(n_iterations=4), backend=backend, dist=dist, checkpoint=ck_dir + "/pr.npz", checkpoint_every=2)
+    dist.barrier()
+    pr2 = run_pagerank(e, PageRankConfig(), backend=backend, dist=dist, checkpoint=ck_dir + "/pr.npz", checkpoint_every=5,
+                       resume=True)
+    out["pagerank_resumed"] = {str(k): v for k, v in pr2.items()}
+    cfg_full = LogisticConfig.for_algo("easgd", n_iterations=12, seed=0)
+    init = LogisticInit.draw("easgd", data.dim, cfg_full.n_slices, 0)
+    run_logistic(data, LogisticConfig.for_algo("easgd", n_iterations=5, seed=0), init, backend=backend, dist=dist,
+                 checkpoint=ck_dir + "/easgd.npz", checkpoint_every=5)
+    dist.barrier()
+    r2 = run_logistic(data, cfg_full, None, backend=backend, dist=dist, checkpoint=ck_dir + "/easgd.npz", resume=True)
+    out["easgd_resumed"] = {"w": r2.w.tolist(), "accs": r2.accs, "bsz": r2.batch_sizes}
+    run_kmeans(pts, KMeansConfig(k=4, n_slices=4, n_iterations=2), backend=backend, dist=dist, checkpoint=ck_dir + "/km.npz",
+               checkpoint_every=1)
+    dist.barrier()
+    km2 = run_kmeans(pts, KMeansConfig(k=4, n_slices=4, n_iterations=4), backend=backend, dist=dist,
+                     checkpoint=ck_dir + "/km.npz", resume=True)
+    out["kmeans_resumed"] = km2.centers.tolist()
     out["mc"] = run_monte_carlo(MonteCarloConfig(n=20001, seed=11), backend="fused" if backend == "fused" else "torch", dist=dist)[1]
     if dist.is_main:
         with open(out_path, "w") as f:

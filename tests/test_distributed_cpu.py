@@ -48,6 +48,16 @@ def test_world_size_independence(runs):
     np.testing.assert_allclose(a["als"]["rmse"], b["als"]["rmse"], rtol=1e-9)
 
 
+def test_resume_under_torchrun(runs):
+    """Checkpoints written and resumed by 1 and by 2 processes reproduce the uninterrupted runs exactly."""
+    for r in runs.values():
+        assert r["pagerank_resumed"].keys() == r["pagerank"].keys()
+        assert max(abs(r["pagerank_resumed"][k] - r["pagerank"][k]) for k in r["pagerank"]) == 0.0
+        assert r["easgd_resumed"]["w"] == r["easgd"]["w"] and r["easgd_resumed"]["accs"] == r["easgd"]["accs"]
+        assert r["easgd_resumed"]["bsz"] == r["easgd"]["bsz"]
+        assert r["kmeans_resumed"] == r["kmeans_syn"]["centers"]
+
+
 def test_matches_oracle(runs, breast_cancer):
     b = runs[2]
     d = breast_cancer
