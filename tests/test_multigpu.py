@@ -58,6 +58,12 @@ def test_reference_scripts_fused_multi_gpu(tmp_path, breast_cancer):
     np.testing.assert_allclose(b["als"]["rmse"], errs, rtol=1e-7)
     from distributed_algorithm_pyspark_b200.models.monte_carlo import accept_count_np
     assert b["mc"] == accept_count_np(0, 20001, 11)
+    # checkpoint / resume through the fused backends (per-rank PageRank files, contribution vector rebuilt in peer memory)
+    assert b["pagerank_resumed"].keys() == b["pagerank"].keys()
+    assert max(abs(b["pagerank_resumed"][k] - v) / v for k, v in b["pagerank"].items()) < 1e-5
+    np.testing.assert_allclose(b["easgd_resumed"]["w"], b["easgd"]["w"], rtol=1e-9)
+    assert b["easgd_resumed"]["bsz"] == b["easgd"]["bsz"]
+    np.testing.assert_allclose(b["kmeans_resumed"], b["kmeans_syn"]["centers"], rtol=1e-9)
 
 
 def test_engines_fused_vs_nccl_multi_gpu(tmp_path):
