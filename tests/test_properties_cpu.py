@@ -94,3 +94,21 @@ def test_hub_split_is_a_lossless_rearrangement(lens, threshold, chunk):
         rebuilt[r] = hub.col[int(hub.ptr[i]):int(hub.ptr[i + 1])].tolist()
     for r in range(len(lens)):
         assert rebuilt[r] == list(range(int(row_ptr[r]), int(row_ptr[r + 1])))
+
+
+@given(st.lists(st.integers(0, 500), min_size=1, max_size=200), st.integers(1, 8), st.floats(0, 64), st.floats(0.1, 2.0))
+@settings(max_examples=80, deadline=None, suppress_health_check=list(HealthCheck))
+def test_vertex_bounds_cover_the_range_and_balance_cost(indeg, world, vertex_cost, hub_edge_cost):
+    """balanced_vertex_bounds: monotone cuts from 0 to V, and no rank's modelled cost exceeds the ideal share by more than
+    the cost of one vertex (cuts fall on vertex boundaries)."""
+    import torch
+    from distributed_algorithm_pyspark_b200.models.pagerank import balanced_vertex_bounds
+    deg = torch.tensor(indeg, dtype=torch.int64)
+    b = balanced_vertex_bounds(deg, world, vertex_cost=vertex_cost, hub_threshold=64, hub_edge_cost=hub_edge_cost)
+    assert len(b) == world + 1 and b[0] == 0 and b[-1] == len(indeg)
+    assert all(b[i] <= b[i + 1] for i in range(world))
+    d = deg.double()
+    cost = torch.where(deg > 64, d * hub_edge_cost, d) + vertex_cost * (deg > 0) + 1
+    total, biggest = float(cost.sum()), float(cost.max())
+    for r in range(world):
+        assert float(cost[b[r]:b[r + 1]].sum()) <= total / world + biggest + 1e-6
