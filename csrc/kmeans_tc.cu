@@ -29,11 +29,16 @@
 // at 59 cycles per MMA instead of 32.  The last super tile is always processed in full (tiles beyond the data
 // re-read the last tile, outputs are masked).
 //
-// What bounds it: every distance must leave TMEM as 4 bytes, and TMEM reads run at ~64 B/clk per SM
-// (B300_MICROARCH.md "LDTM throughput"): a 128 x 1024 tile is 512 KB = 8192 cycles of tcgen05.ld against 4096 cycles
-// of MMA (K is only 128).  Three different epilogue instruction mixes (88, 88 and 62 instructions per 32 columns)
-// all measured 7700-7900 cycles per tile -- the kernel sits on that TMEM-read roofline, and the cheaper epilogue
-// pays off only through the power budget (higher sustained clock: 36.7 -> 34.4 ms per iteration on 125M x 128).
+// What bounds it (two candidates, the last ncu capture favours the second):
+//  (a) every distance must leave TMEM as 4 bytes and TMEM reads run at ~64 B/clk per SM (B300_MICROARCH.md "LDTM
+//      throughput"): a 128 x 1024 tile is 512 KB = 8192 cycles of tcgen05.ld against 4096 cycles of MMA (K is only 128);
+//  (b) the shared-memory data pipe: the raw ncu report shows LSU shared-memory wavefronts at 47 % of peak (the broadcast
+//      LDS.128 of the norms cost ~3.6 wavefronts each, 231 M in total) next to 52 % for the tensor core's own operand
+//      reads -- 99 % together.
+// Three different epilogue instruction mixes (88, 88 and 62 instructions per 32 columns, all with the SAME number of
+// norm loads) measured 7700-7900 cycles per tile, which fits both; the cheaper epilogue paid off only through the power
+// budget (higher sustained clock: 36.7 -> 34.4 ms per iteration on 125M x 128).  Next experiment: fewer / cheaper norm
+// loads (ROADMAP.md).
 //
 // Near-ties: distances are compared at a resolution of 2^(E-23) <= 4 M * 2^-23 (M = bound on |distance|), far below
 // the error already introduced by bf16 inputs; exact tie semantics need the CUDA-core path (kmeans.cu).
