@@ -66,23 +66,46 @@ def bench_kmeans(dist, backend, n=125_000_000, d=128, k=1024, iters=3, warmup=1)
     return out
 
 
-def bench_pagerank(dist, backend, scale=24, edge_factor=16, iters=10, warmup=2):
-    """BASELINE.json config 4: R-MAT power-law graph, GTEPS = de-duplicated edges * iterations / time."""
+def bench_pagerank(dist, backend, scale=26, edge_factor=16, iters=30, warmup=1, stats=True, tag="pagerank"):
+    """BASELINE.json config 4: R-MAT scale-26 (edge factor 16), 30 iterations; GTEPS = de-duplicated edges * iterations /
+    time.  The fused backend runs the 30 iterations as ONE persistent launch (``ShardedPageRank.run``); a second,
+    untimed run collects the in-kernel %globaltimer stamps for the per-rank breakdown."""
     import torch
     from distributed_algorithm_pyspark_b200.config import PageRankConfig
     from distributed_algorithm_pyspark_b200.data.datasets import rmat_edges_device
     from distributed_algorithm_pyspark_b200.models.pagerank import ShardedPageRank, build_sharded_graph
     dev = dist.device
+    fused = backend == "fused"
+    copies = None
+    if fused and dist.world > 1:
+        from distributed_algorithm_pyspark_b200.parallel.symm import default_heap
+        heap = default_heap(max(1 << 30, 2 * (1 << scale) * 4 + (64 << 20)))
+        copies = 1 if heap.multicast else dist.world - 1
     src, dst = rmat_edges_device(scale, edge_factor, dev, seed=1)
-    g = build_sharded_graph(src, dst, 1 << scale, dist)
+    g = build_sharded_graph(src, dst, 1 << scale, dist, push_copies=copies)
     del src, dst
     torch.cuda.empty_cache()
-    pr = ShardedPageRank(g, PageRankConfig(n_iterations=iters), dist, backend="fused" if backend == "fused" else "nccl")
-    ms = _timed(dist, pr.step, iters, warmup)
+    pr = ShardedPageRank(g, PageRankConfig(n_iterations=iters), dist, backend="fused" if fused else "nccl")
+    ms = _timed(dist, lambda: pr.run(iters), 1, warmup) / iters
     pr.finish()
-    out = {"pagerank_gteps": g.n_edges / (ms / 1e3) / 1e9, "pagerank_ms_per_iter": ms, "pagerank_scale": scale,
-           "pagerank_edges_dedup": g.n_edges, "pagerank_row_blocks": int(g.blocks.numel() - 1),
-           "pagerank_local_nnz": int(g.col_idx.numel()), "pagerank_local_vertices": int(g.v1 - g.v0)}
+    out = {f"{tag}_gteps": g.n_edges / (ms / 1e3) / 1e9, f"{tag}_ms_per_iter": ms, f"{tag}_scale": scale,
+           f"{tag}_iterations": iters, f"{tag}_edges_dedup": g.n_edges}
+    if fused:
+        out[f"{tag}_launches_per_run"] = 1
+        out[f"{tag}_multicast"] = bool(dist.world > 1 and pr.heap.multicast)
+    if fused and stats:
+        pr._collect_stats = True
+        pr.reset()
+        pr.run(iters)
+        pr.finish()
+        st = pr.stats.double().cpu()                       # [iters, 4] ns: enter, wait passed, last ticket, published
+        mine = {"rank": dist.rank, "local_vertices": int(g.v1 - g.v0), "local_nnz": int(g.col_idx.numel() + g.hub.col.numel()),
+                "push_bytes_per_iter": pr.push_bytes_per_iter(),
+                "flag_wait_us_mean": float((st[1:, 1] - st[1:, 0]).mean() / 1e3),
+                "compute_us_mean": float((st[1:, 2] - st[1:, 1]).mean() / 1e3),
+                "publish_us_mean": float((st[1:, 3] - st[1:, 2]).mean() / 1e3),
+                "iter_us_mean": float((st[1:, 0] - st[:-1, 0]).mean() / 1e3)}
+        out[f"{tag}_per_rank"] = dist.all_gather_object(mine)
     del pr, g
     torch.cuda.empty_cache()
     return out
@@ -185,12 +208,13 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default="")
     ap.add_argument("--impl", default="ours", choices=["ours", "nccl"])
-    ap.add_argument("--pagerank-scale", type=int, default=24)
+    ap.add_argument("--pagerank-scale", type=int, default=26)
+    ap.add_argument("--pagerank-iters", type=int, default=30)
     a = ap.parse_args()
     from distributed_algorithm_pyspark_b200.parallel.dist import init_distributed, shutdown
     dist = init_distributed()
     only = [s for s in a.only.split(",") if s] or None
-    out = run_all(dist, "fused" if a.impl == "ours" else "nccl", only, pagerank={"scale": a.pagerank_scale})
+    out = run_all(dist, "fused" if a.impl == "ours" else "nccl", only, pagerank={"scale": a.pagerank_scale, "iters": a.pagerank_iters})
     out["impl"], out["n_gpus"] = a.impl, dist.world
     if dist.is_main:
         print(json.dumps(out))

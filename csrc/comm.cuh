@@ -32,12 +32,59 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
   return t;
 }
 
+// ---- NVLS multicast (multimem.*) wrappers -----------------------------------------------------------------------
+// `p` must be an address inside the multicast mapping DapbComm::mc_heap.  A multimem store is replicated by the
+// NVSwitch into every rank's copy of the heap (one NVLink egress instead of W - 1); ld_reduce pulls the W copies and
+// adds them inside the switch; red adds the operand into every copy.
+__device__ __forceinline__ void multimem_st(float* p, float v) {
+  asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" :: "l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_st(double* p, double v) {
+  asm volatile("multimem.st.relaxed.sys.global.f64 [%0], %1;" :: "l"(p), "d"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_st(uint64_t* p, uint64_t v) {
+  asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_st(float4* p, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float4* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float multimem_ld_reduce_add(const float* p) {
+  float v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ double multimem_ld_reduce_add(const double* p) {
+  double v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_red_add(float* p, float v) {
+  asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" :: "l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_red_add(unsigned long long* p, unsigned long long v) {
+  asm volatile("multimem.red.relaxed.sys.global.add.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+
 // Heap layout: [0, DAPB_FLAG_BYTES) = uint64 flag words, rest = payload.
 __device__ __forceinline__ uint64_t* comm_flags(const DapbComm& c, int r) {
   return reinterpret_cast<uint64_t*>(c.heap[r]);
 }
 __device__ __forceinline__ char* comm_payload(const DapbComm& c, int r, uint64_t off) {
   return reinterpret_cast<char*>(c.heap[r]) + DAPB_FLAG_BYTES + off;
+}
+// multicast alias of the payload (only valid when c.mc_heap != nullptr)
+__device__ __forceinline__ char* comm_payload_mc(const DapbComm& c, uint64_t off) {
+  return reinterpret_cast<char*>(c.mc_heap) + DAPB_FLAG_BYTES + off;
+}
+__device__ __forceinline__ uint64_t* comm_flags_mc(const DapbComm& c) {
+  return reinterpret_cast<uint64_t*>(c.mc_heap);
 }
 
 // Spin until the local flag reaches `epoch`.  A dead peer must not hang the GPU forever
@@ -137,13 +184,53 @@ __device__ __forceinline__ void block_barrier(const DapbComm& c, int my_rank, ui
 
 // ---------------------------------------------------------------------------------------------
 // All-gather push helper: a thread that produced element `idx` of the gathered vector stores it
-// into the same offset of every rank's copy (local copy included).
+// into the same offset of every rank's copy (local copy included): ONE multimem.st when the heap
+// has a multicast mapping (the switch replicates it), else W unicast stores issued back to back.
 // ---------------------------------------------------------------------------------------------
 template <typename T>
 __device__ __forceinline__ void push_all(const DapbComm& c, uint64_t off, uint64_t idx, T v) {
-#pragma unroll 1
-  for (int r = 0; r < c.world; ++r)
-    reinterpret_cast<T*>(comm_payload(c, r, off))[idx] = v;
+  if (c.mc_heap != nullptr) {
+    multimem_st(reinterpret_cast<T*>(comm_payload_mc(c, off)) + idx, v);
+    return;
+  }
+#pragma unroll
+  for (int r = 0; r < DAPB_MAX_RANKS; ++r)
+    if (r < c.world) reinterpret_cast<T*>(comm_payload(c, r, off))[idx] = v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Grid-wide collectives over a payload region that every rank has ALREADY FILLED LOCALLY with its
+// contribution (n elements at `off` of its own heap) and published with a barrier:
+//   * grid_reduce_scatter_allgather: two-shot all-reduce.  Rank r owns elements [r*seg, (r+1)*seg);
+//     it reduces them over all ranks (multimem.ld_reduce, or W peer loads added in RANK ORDER) and
+//     broadcasts the sums (multimem.st, or W peer stores), so every rank ends with bit-identical
+//     values.  Work is spread over the whole grid (threads stride over float4 groups).
+// The caller brackets it with rank barriers (data in place before, results landed after).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void grid_twoshot_allreduce_f32(const DapbComm& c, uint64_t off, int n /* multiple of 4*world */,
+                                                           int64_t gtid, int64_t gthreads) {
+  const int seg4 = n / 4 / c.world;                   // float4 groups owned by each rank
+  const int64_t base4 = (int64_t)c.rank * seg4;
+  if (c.mc_heap != nullptr) {
+    float4* mc = reinterpret_cast<float4*>(comm_payload_mc(c, off));
+    for (int64_t i = gtid; i < seg4; i += gthreads) {
+      const float4 v = multimem_ld_reduce_add(mc + base4 + i);
+      multimem_st(mc + base4 + i, v);
+    }
+  } else {
+    for (int64_t i = gtid; i < seg4; i += gthreads) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < DAPB_MAX_RANKS; ++r)
+        if (r < c.world) {
+          const float4 v = __ldcg(reinterpret_cast<const float4*>(comm_payload(c, r, off)) + base4 + i);
+          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+#pragma unroll
+      for (int r = 0; r < DAPB_MAX_RANKS; ++r)
+        if (r < c.world) reinterpret_cast<float4*>(comm_payload(c, r, off))[base4 + i] = acc;
+    }
+  }
 }
 
 }  // namespace dapb

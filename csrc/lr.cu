@@ -989,6 +989,26 @@ __global__ void lr_eval_kernel(const T* X, const float* y, int64_t n, int D, con
 }
 }  // namespace
 
+// Bernoulli keep flags of one iteration as a byte mask (the same Philox decision the step kernels take in-line).
+// Not used by the fused path -- it lets the PyTorch+NCCL BASELINE sample the identical mini-batch at memory speed.
+namespace {
+__global__ void philox_mask_kernel(int64_t row_base, int64_t n, uint64_t seed, uint32_t iteration, uint32_t threshold24,
+                                   uint8_t* out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = threshold24 >= (1u << 24) ? 1 : (uint8_t)philox_keep_row((uint64_t)(row_base + i), iteration, seed, threshold24);
+}
+}  // namespace
+extern "C" int dapb_philox_mask(int64_t row_base, int64_t n_rows, uint64_t seed, uint32_t iteration, uint32_t threshold24,
+                                uint8_t* out, void* stream) {
+  DAPB_REQUIRE(n_rows >= 0 && out != nullptr, "philox_mask: bad arguments");
+  if (n_rows == 0) return 0;
+  int64_t blocks = (n_rows + 255) / 256;
+  if (blocks > dapb::sm_count() * 16) blocks = dapb::sm_count() * 16;
+  philox_mask_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(row_base, n_rows, seed, iteration, threshold24, out);
+  DAPB_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" int dapb_lr_eval(const void* X, const float* y, int64_t n_rows, int32_t D, int32_t dtype,
                             const float* w, float eps, float* acc_out, uint32_t* scratch2, void* stream) {
   DAPB_REQUIRE(n_rows > 0 && D > 0 && scratch2 && acc_out, "lr_eval: bad arguments");

@@ -111,6 +111,166 @@ extern "C" int dapb_barrier(const DapbComm* comm, uint32_t flag_base, uint64_t e
   return 0;
 }
 
+// ------------------------------------------------------------------ stand-alone grid-wide collectives (F8)
+// Multi-CTA versions for messages beyond one CTA's reach (KBs .. 100s of MBs).  All are cooperative launches (the grid
+// synchronises around the cross-rank flag barriers) and use the multicast mapping when the heap has one:
+//   all-gather       every element is pushed once (multimem.st) or W times (unicast) by the thread that read it
+//   reduce-scatter   owner pulls its segment from all ranks (multimem.ld_reduce, or W peer loads summed in rank order)
+//   two-shot all-reduce = reduce-scatter + all-gather in place, bit-identical on all ranks
+//   all-to-all       rank r stores block d of its send buffer into slot r of rank d
+// Each call consumes TWO barrier epochs on its flag words: 2*epoch - 1 and 2*epoch.
+namespace {
+
+__device__ __forceinline__ void grid_rank_barrier(const DapbComm& c, uint32_t flag_base, uint64_t epoch,
+                                                  cg::grid_group& grid) {
+  grid.sync();
+  if (blockIdx.x == 0) block_barrier(c, c.rank, flag_base, epoch);
+  grid.sync();
+}
+
+template <typename T>
+__global__ void allgather_kernel(DapbComm c, uint64_t off, uint32_t flag_base, uint64_t epoch, const T* src,
+                                 T* dst, int64_t n) {
+  cg::grid_group grid = cg::this_grid();
+  const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, gth = (int64_t)gridDim.x * blockDim.x;
+  grid_rank_barrier(c, flag_base, 2 * epoch - 1, grid);           // everybody finished reading the previous result
+  for (int64_t i = gtid; i < n; i += gth) push_all<T>(c, off, (uint64_t)c.rank * n + i, src[i]);
+  __threadfence_system();
+  grid_rank_barrier(c, flag_base, 2 * epoch, grid);
+  const T* mine = reinterpret_cast<const T*>(comm_payload(c, c.rank, off));
+  for (int64_t i = gtid; i < n * c.world; i += gth) dst[i] = __ldcg(mine + i);
+}
+
+// mode 0: reduce-scatter (dst[n/world] = my segment), mode 1: all-reduce (dst[n])
+__global__ void twoshot_kernel(DapbComm c, uint64_t off, uint32_t flag_base, uint64_t epoch, const float* src,
+                               float* dst, int n, int mode) {
+  cg::grid_group grid = cg::this_grid();
+  const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, gth = (int64_t)gridDim.x * blockDim.x;
+  float4* mine = reinterpret_cast<float4*>(comm_payload(c, c.rank, off));
+  for (int64_t i = gtid; i < n / 4; i += gth) mine[i] = reinterpret_cast<const float4*>(src)[i];
+  __threadfence_system();
+  grid_rank_barrier(c, flag_base, 2 * epoch - 1, grid);
+  grid_twoshot_allreduce_f32(c, off, n, gtid, gth);
+  __threadfence_system();
+  grid_rank_barrier(c, flag_base, 2 * epoch, grid);
+  if (mode == 1) {
+    for (int64_t i = gtid; i < n / 4; i += gth) reinterpret_cast<float4*>(dst)[i] = __ldcg(mine + i);
+  } else {
+    const int seg4 = n / 4 / c.world;
+    for (int64_t i = gtid; i < seg4; i += gth) reinterpret_cast<float4*>(dst)[i] = __ldcg(mine + (int64_t)c.rank * seg4 + i);
+  }
+}
+
+__global__ void alltoall_kernel(DapbComm c, uint64_t off, uint32_t flag_base, uint64_t epoch,
+                                const unsigned long long* src, unsigned long long* dst, int64_t n) {
+  cg::grid_group grid = cg::this_grid();
+  const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, gth = (int64_t)gridDim.x * blockDim.x;
+  grid_rank_barrier(c, flag_base, 2 * epoch - 1, grid);
+  for (int d = 0; d < c.world; ++d) {
+    unsigned long long* slot = reinterpret_cast<unsigned long long*>(comm_payload(c, d, off)) + (int64_t)c.rank * n;
+    for (int64_t i = gtid; i < n; i += gth) slot[i] = src[(int64_t)d * n + i];
+  }
+  __threadfence_system();
+  grid_rank_barrier(c, flag_base, 2 * epoch, grid);
+  const unsigned long long* mine = reinterpret_cast<const unsigned long long*>(comm_payload(c, c.rank, off));
+  for (int64_t i = gtid; i < n * c.world; i += gth) dst[i] = __ldcg(mine + i);
+}
+
+template <typename K>
+int coop_launch(K kernel, void** kargs, int threads, cudaStream_t st, int64_t work) {
+  int per_sm = 0;
+  DAPB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0));
+  int64_t grid = (int64_t)per_sm * dapb::sm_count();
+  const int64_t need = (work + threads - 1) / threads;
+  if (grid > need) grid = need;
+  if (grid < 1) grid = 1;
+  DAPB_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)kernel, dim3((unsigned)grid), dim3(threads), kargs, 0, st));
+  return 0;
+}
+
+int check_grid_coll(const DapbComm* comm, uint64_t off, uint64_t bytes, uint64_t epoch, const char* what) {
+  DAPB_REQUIRE(comm && comm->world >= 1 && comm->world <= DAPB_MAX_RANKS, "%s: bad comm", what);
+  DAPB_REQUIRE(epoch >= 1, "%s: epoch must start at 1", what);
+  DAPB_REQUIRE(DAPB_FLAG_BYTES + off + bytes <= comm->heap_bytes, "%s: heap too small (%llu > %llu)", what,
+               (unsigned long long)(DAPB_FLAG_BYTES + off + bytes), (unsigned long long)comm->heap_bytes);
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int dapb_allgather(const DapbComm* comm, uint64_t off, uint32_t flag_base, uint64_t epoch, const void* src,
+                              void* dst, int64_t n_per_rank, int32_t elem_bytes, void* stream) {
+  DAPB_REQUIRE(elem_bytes == 4 || elem_bytes == 8, "allgather: 4- or 8-byte elements");
+  if (int rc = check_grid_coll(comm, off, (uint64_t)comm->world * n_per_rank * elem_bytes, epoch, "allgather")) return rc;
+  DapbComm c = *comm;
+  void* kargs[] = {&c, &off, &flag_base, &epoch, &src, &dst, &n_per_rank};
+  if (elem_bytes == 4) return coop_launch(allgather_kernel<float>, kargs, 256, (cudaStream_t)stream, n_per_rank * c.world);
+  return coop_launch(allgather_kernel<double>, kargs, 256, (cudaStream_t)stream, n_per_rank * c.world);
+}
+static int twoshot(const DapbComm* comm, uint64_t off, uint32_t flag_base, uint64_t epoch, const float* src, float* dst,
+                   int32_t n, int mode, void* stream, const char* what) {
+  if (int rc = check_grid_coll(comm, off, (uint64_t)n * 4, epoch, what)) return rc;
+  DAPB_REQUIRE(n > 0 && n % (4 * comm->world) == 0, "%s: n must be a multiple of 4 * world", what);
+  DAPB_REQUIRE(((uintptr_t)src & 15) == 0 && ((uintptr_t)dst & 15) == 0 && (off & 15) == 0, "%s: 16-byte alignment", what);
+  DapbComm c = *comm;
+  void* kargs[] = {&c, &off, &flag_base, &epoch, &src, &dst, &n, &mode};
+  return coop_launch(twoshot_kernel, kargs, 256, (cudaStream_t)stream, n / 4);
+}
+extern "C" int dapb_allreduce_twoshot_f32(const DapbComm* comm, uint64_t off, uint32_t flag_base, uint64_t epoch,
+                                          const float* src, float* dst, int32_t n, void* stream) {
+  return twoshot(comm, off, flag_base, epoch, src, dst, n, 1, stream, "allreduce_twoshot");
+}
+extern "C" int dapb_reduce_scatter_f32(const DapbComm* comm, uint64_t off, uint32_t flag_base, uint64_t epoch,
+                                       const float* src, float* dst, int32_t n, void* stream) {
+  return twoshot(comm, off, flag_base, epoch, src, dst, n, 0, stream, "reduce_scatter");
+}
+extern "C" int dapb_alltoall_u64(const DapbComm* comm, uint64_t off, uint32_t flag_base, uint64_t epoch,
+                                 const unsigned long long* src, unsigned long long* dst, int64_t n_per_pair, void* stream) {
+  if (int rc = check_grid_coll(comm, off, (uint64_t)comm->world * n_per_pair * 8, epoch, "alltoall")) return rc;
+  DapbComm c = *comm;
+  void* kargs[] = {&c, &off, &flag_base, &epoch, &src, &dst, &n_per_pair};
+  return coop_launch(alltoall_kernel, kargs, 256, (cudaStream_t)stream, n_per_pair * c.world);
+}
+
+// ------------------------------------------------------------------ cross-GPU flag-protocol stress
+// ONE CTA per rank runs `iters` back-to-back one-shot all-reduces on real peers (NVLink ordering, not one GPU's L2),
+// with pseudo-random __nanosleep skew between epochs so that fast ranks run a full epoch ahead of slow ones and the
+// double-buffered slots / monotonic flags are exercised; every element of every epoch is checked bit for bit.
+__global__ void allreduce_stress_kernel(DapbComm c, uint64_t off, uint32_t flag_base, uint64_t epoch0, int n, int iters,
+                                        uint32_t seed, int* out_fail) {
+  extern __shared__ float sm[];
+  float* src = sm;
+  float* dst = sm + n;
+  int fails = 0;
+  uint32_t rng = seed * 2654435761u + (uint32_t)c.rank * 40503u + 1u;
+  for (int it = 0; it < iters; ++it) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) src[i] = (float)((c.rank + 1) * (i % 7 + 1) + (it & 1023));
+    __syncthreads();
+    block_allreduce_oneshot<float>(c, c.rank, off, flag_base, epoch0 + it, src, dst, n);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      float want = 0.f;
+      for (int r = 0; r < c.world; ++r) want += (float)((r + 1) * (i % 7 + 1) + (it & 1023));
+      if (dst[i] != want) ++fails;
+    }
+    rng = rng * 1664525u + 1013904223u;
+    if ((rng >> 28) == 0) __nanosleep((rng >> 8) & 0x1fff);      // 1 epoch in 16: stall up to 8 us
+    __syncthreads();
+  }
+  if (fails) atomicAdd(out_fail, fails);
+}
+
+extern "C" int dapb_allreduce_stress(const DapbComm* comm, uint64_t off, uint32_t flag_base, uint64_t epoch0, int32_t n,
+                                     int32_t iters, uint32_t seed, int32_t* out_fail, void* stream) {
+  DAPB_REQUIRE(comm && comm->world >= 1 && comm->world <= DAPB_MAX_RANKS, "allreduce_stress: bad comm");
+  DAPB_REQUIRE(n > 0 && n <= 4096 && iters > 0 && epoch0 >= 1, "allreduce_stress: n in [1,4096], iters > 0, epoch0 >= 1");
+  uint64_t need = DAPB_FLAG_BYTES + off + (uint64_t)2 * comm->world * ((n + 3) & ~3) * sizeof(float);
+  DAPB_REQUIRE(comm->world == 1 || need <= comm->heap_bytes, "allreduce_stress: heap too small");
+  allreduce_stress_kernel<<<1, 256, 2 * n * sizeof(float), (cudaStream_t)stream>>>(*comm, off, flag_base, epoch0, n, iters,
+                                                                                   seed, out_fail);
+  DAPB_LAUNCH_CHECK();
+  return 0;
+}
+
 // ------------------------------------------------------------------ single-GPU protocol test
 // `world` CTAs of one cooperative launch play the ranks (B200_PROFILING.md: never emulate ranks
 // with separate launches that wait on each other on one GPU).
@@ -123,6 +283,7 @@ __global__ void comm_selftest_kernel(char* heaps, uint64_t heap_bytes, int world
   c.rank = blockIdx.x;
   c.world = world;
   c.heap_bytes = heap_bytes;
+  c.mc_heap = nullptr;
   for (int r = 0; r < DAPB_MAX_RANKS; ++r) c.heap[r] = r < world ? heaps + (uint64_t)r * heap_bytes : nullptr;
   int fails = 0;
   for (int it = 1; it <= iters; ++it) {

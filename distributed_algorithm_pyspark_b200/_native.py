@@ -21,13 +21,23 @@ _load_error: Optional[str] = None
 
 class DapbComm(C.Structure):
     _fields_ = [("rank", C.c_int32), ("world", C.c_int32),
-                ("heap", C.c_void_p * MAX_RANKS), ("heap_bytes", C.c_uint64)]
+                ("heap", C.c_void_p * MAX_RANKS), ("heap_bytes", C.c_uint64), ("mc_heap", C.c_void_p)]
 
 
 class DapbPrHub(C.Structure):
     _fields_ = [("hub_rows", C.c_void_p), ("hub_col", C.c_void_p), ("chunk_start", C.c_void_p),
                 ("chunk_end", C.c_void_p), ("hub_chunk_ptr", C.c_void_p), ("chunk_partial", C.c_void_p),
-                ("n_hub", C.c_int32), ("n_chunks", C.c_int32)]
+                ("n_hub", C.c_int32), ("n_chunks", C.c_int32), ("chunk_row", C.c_void_p), ("row_done", C.c_void_p)]
+
+
+class DapbPrRunArgs(C.Structure):
+    _fields_ = [("row_ptr", C.c_void_p), ("col_idx", C.c_void_p), ("inv_outdeg", C.c_void_p), ("blocks", C.c_void_p),
+                ("n_blocks", C.c_int32), ("f64", C.c_int32),
+                ("nv_local", C.c_int64), ("v0", C.c_int64), ("V", C.c_int64),
+                ("base", C.c_double), ("damp", C.c_double),
+                ("ranks_local", C.c_void_p), ("c_off", C.c_uint64), ("flag_base", C.c_uint32), ("epoch0", C.c_uint64),
+                ("n_iters", C.c_int32), ("it0", C.c_int32), ("wait_first", C.c_int32), ("skip_empty_ok", C.c_int32),
+                ("grid", C.c_int32), ("sync", C.c_void_p), ("stats", C.c_void_p), ("hub", DapbPrHub)]
 
 
 class DapbLrParityArgs(C.Structure):
@@ -89,10 +99,16 @@ def _declare(lib: C.CDLL):
         "dapb_allreduce_f32": (C.c_int, [P(DapbComm), u64, u32, u64, vp, vp, i32, vp]),
         "dapb_allreduce_f64": (C.c_int, [P(DapbComm), u64, u32, u64, vp, vp, i32, vp]),
         "dapb_barrier": (C.c_int, [P(DapbComm), u32, u64, vp]),
+        "dapb_allreduce_stress": (C.c_int, [P(DapbComm), u64, u32, u64, i32, i32, u32, vp, vp]),
+        "dapb_allgather": (C.c_int, [P(DapbComm), u64, u32, u64, vp, vp, i64, i32, vp]),
+        "dapb_allreduce_twoshot_f32": (C.c_int, [P(DapbComm), u64, u32, u64, vp, vp, i32, vp]),
+        "dapb_reduce_scatter_f32": (C.c_int, [P(DapbComm), u64, u32, u64, vp, vp, i32, vp]),
+        "dapb_alltoall_u64": (C.c_int, [P(DapbComm), u64, u32, u64, vp, vp, i64, vp]),
         "dapb_lr_parity_run": (C.c_int, [P(DapbLrParityArgs), P(DapbComm), vp]),
         "dapb_lr_parity_payload_bytes": (u64, [i32, i32]),
         "dapb_lr_step": (C.c_int, [P(DapbLrStepArgs), P(DapbComm), vp]),
         "dapb_lr_step_tc": (C.c_int, [P(DapbLrStepArgs), P(DapbComm), vp]),
+        "dapb_philox_mask": (C.c_int, [i64, i64, u64, u32, u32, vp, vp]),
         "dapb_lr_eval": (C.c_int, [vp, vp, i64, i32, i32, vp, f32, vp, vp, vp]),
         "dapb_mc_pi": (C.c_int, [u64, u64, u64, vp, vp]),
         "dapb_kmeans_assign": (C.c_int, [vp, i64, i32, i32, vp, i32, vp, vp, vp, vp]),
@@ -101,11 +117,10 @@ def _declare(lib: C.CDLL):
         "dapb_kmeans_tc_prepare": (C.c_int, [vp, i32, i32, vp, vp, C.c_float, vp]),
         "dapb_kmeans_assign_tc": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, vp, vp, i32, vp]),
         "dapb_kmeans_assign_tc_dbg": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, vp, vp, i32, vp, vp]),
-        "dapb_pagerank_init": (C.c_int, [P(DapbComm), vp, i64, i64, i64, f32, u64, vp]),
+        "dapb_pagerank_init": (C.c_int, [P(DapbComm), vp, i64, i64, i64, f64, u64, i32, vp]),
         "dapb_pagerank_step": (C.c_int, [P(DapbComm), vp, vp, vp, vp, i32, i64, i64, i64, f32, f32, vp,
                                          u64, u32, u64, vp, i32, i32, i32, vp]),
-        "dapb_pagerank_step_v2": (C.c_int, [P(DapbComm), vp, vp, vp, vp, i32, i64, i64, i64, P(DapbPrHub), f32, f32, vp,
-                                            u64, u32, u64, vp, i32, i32, i32, vp]),
+        "dapb_pagerank_run": (C.c_int, [P(DapbPrRunArgs), P(DapbComm), vp]),
         "dapb_tc_seed": (C.c_int, [vp, i64, vp, u64, vp, vp, i32, i32, vp]),
         "dapb_tc_expand": (C.c_int, [P(DapbComm), vp, vp, vp, i64, vp, u64, vp, vp, u64, u64, vp]),
         "dapb_tc_exchange": (C.c_int, [P(DapbComm), vp, u64, u64, u32, u64, vp]),

@@ -131,10 +131,16 @@ class ShardedKMeans:
                                                         self.region.flag_base, self.region.next_epoch(),
                                                         self.counts_out.data_ptr(), 1, st), "kmeans_finalize")
         else:
-            a = self._assign_torch()
+            # baseline: chunked cuBLAS distances + arg-min + index_add_ (chunks of ~0.5 M rows keep the launches few
+            # and the [chunk, k] distance tile at a few GB), then one NCCL all-reduce
             sums = torch.zeros(self.k, self.d, dtype=self.acc_dtype, device=self.X.device)
-            sums.index_add_(0, a, self.X.to(self.acc_dtype))
-            cnt = torch.bincount(a, minlength=self.k).to(self.acc_dtype)
+            cnt = torch.zeros(self.k, dtype=torch.int64, device=self.X.device)
+            chunk = self._chunk_rows()
+            for i in range(0, self.n, chunk):
+                a = self._assign_torch(i, min(self.n, i + chunk))
+                sums.index_add_(0, a, self.X[i:i + chunk].to(self.acc_dtype))
+                cnt += torch.bincount(a, minlength=self.k)
+            cnt = cnt.to(self.acc_dtype)
             buf = torch.cat([sums, cnt[:, None]], dim=1)
             self.dist.all_reduce_sum(buf)
             sums, cnt = buf[:, :-1], buf[:, -1]
@@ -142,23 +148,29 @@ class ShardedKMeans:
             self.centers[has] = sums[has] / cnt[has][:, None]
             self.counts_out.copy_(cnt.to(torch.int32))
 
-    def _assign_torch(self) -> torch.Tensor:
-        out = torch.empty(self.n, dtype=torch.int64, device=self.X.device)
-        Cc = self.centers
-        chunk = max(1, (64 << 20) // max(self.k * 8, 1))
+    def _chunk_rows(self) -> int:
         if self.X.dtype == torch.float64:
-            for i in range(0, self.n, chunk):                      # exact (x-c)^2 form for parity data
-                x = self.X[i:i + chunk]
-                dmat = ((x[:, None, :] - Cc[None, :, :]) ** 2).sum(-1)
-                out[i:i + chunk] = dmat.argmin(dim=1)
+            return max(1, (64 << 20) // max(self.k * self.d * 8, 1))      # [chunk, k, d] broadcast tile
+        return max(1, (2 << 30) // max(self.k * 4, 1))                     # [chunk, k] fp32 distance tile of 2 GB
+
+    def _assign_torch(self, lo: int = 0, hi: Optional[int] = None) -> torch.Tensor:
+        """Assignment of rows [lo, hi) (default: all rows, chunked)."""
+        if hi is None:
+            hi = self.n
+        Cc = self.centers
+        chunk = self._chunk_rows()
+        outs = []
+        if self.X.dtype == torch.float64:
+            for i in range(lo, hi, chunk):                         # exact (x-c)^2 form for parity data
+                x = self.X[i:min(hi, i + chunk)]
+                outs.append(((x[:, None, :] - Cc[None, :, :]) ** 2).sum(-1).argmin(dim=1))
         else:
             cn = (Cc * Cc).sum(1)
             Cm = Cc.to(self.X.dtype)
-            for i in range(0, self.n, chunk):
-                x = self.X[i:i + chunk]
-                dmat = cn[None, :] - 2.0 * (x @ Cm.T).float()
-                out[i:i + chunk] = dmat.argmin(dim=1)
-        return out
+            for i in range(lo, hi, chunk):
+                x = self.X[i:min(hi, i + chunk)]
+                outs.append((cn[None, :] - 2.0 * (x @ Cm.T).float()).argmin(dim=1))
+        return outs[0] if len(outs) == 1 else (torch.cat(outs) if outs else torch.empty(0, dtype=torch.int64, device=self.X.device))
 
     def assign(self) -> torch.Tensor:
         """Assignment of the local points under the current centres (int64)."""

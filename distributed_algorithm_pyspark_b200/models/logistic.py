@@ -408,23 +408,37 @@ class ShardedLogisticEngine:
         g = (r.to(Xs.dtype) @ Xs).float()
         return g, idx.numel()
 
+    def _keep_mask_nccl(self) -> torch.Tensor:
+        """The step's Bernoulli mask for the baseline.  On a GPU it comes from the library's one-pass Philox mask
+        kernel (33 M rows in tens of microseconds), so the baseline's step time is its gather + two GEMVs +
+        all-reduce and not an emulated RNG; on CPU (gloo tests) the torch int64 emulation is used."""
+        cfg = self.cfg
+        if cfg.algo == "gd":
+            return torch.ones(self.n_rows, dtype=torch.bool, device=self.X.device)
+        if self.X.is_cuda and _native.available():
+            if getattr(self, "_mask_buf", None) is None or self._mask_buf.numel() < self.n_rows:
+                self._mask_buf = torch.empty(self.n_rows, dtype=torch.uint8, device=self.X.device)
+            _native.check(_native.load().dapb_philox_mask(self.row_base, self.n_rows, cfg.sample_seed, self.t,
+                                                          self.threshold24, self._mask_buf.data_ptr(),
+                                                          _native.stream_ptr()), "philox_mask")
+            return self._mask_buf[:self.n_rows].view(torch.bool)
+        return philox_row_mask_torch(self.n_rows, cfg.mini_batch_fraction, cfg.sample_seed, self.t,
+                                     self.row_base, device=self.X.device)
+
     def _step_nccl(self):
         cfg, d = self.cfg, self.dist
-        if cfg.algo == "gd":
-            keep = torch.ones(self.n_rows, dtype=torch.bool, device=self.X.device)
-        else:
-            keep = philox_row_mask_torch(self.n_rows, cfg.mini_batch_fraction, cfg.sample_seed, self.t,
-                                         self.row_base, device=self.X.device)
+        keep = self._keep_mask_nccl()
         if cfg.algo in ("ssgd", "gd"):
             g, cnt = self._grad_nccl(self.w, keep)
-            buf = torch.cat([g, torch.tensor([float(cnt)], device=g.device)])
+            buf = torch.cat([g, torch.full((1,), float(cnt), device=g.device)])
             d.all_reduce_sum(buf)
-            g, cnt_tot = buf[:-1], float(buf[-1].item())
+            g, cnt_tot = buf[:-1], buf[-1]                         # stays on the device: no host round trip
             if cfg.algo == "gd":
                 self.w -= cfg.eta * g
-            elif cnt_tot > 0:
-                self.w -= cfg.eta * (g / cnt_tot + cfg.lam * _reg_gradient_t(self.w, cfg.reg_type, cfg.reg_alpha))
-            self.last_count.fill_(int(cnt_tot))
+            else:
+                upd = cfg.eta * (g / cnt_tot.clamp(min=1.0) + cfg.lam * _reg_gradient_t(self.w, cfg.reg_type, cfg.reg_alpha))
+                self.w -= torch.where(cnt_tot > 0, upd, torch.zeros_like(upd))
+            self.last_count.copy_(cnt_tot.to(torch.int32).reshape(1))
             return
         alpha, beta = cfg.eta * cfg.rho, self.P * cfg.eta * cfg.rho
         if cfg.algo != "easgd":

@@ -6,7 +6,9 @@ form of :52-57 including the reference's "absent vertex" rule
 
 Backends: ``oracle`` (Python floats, bit-exact with the values recorded in pagerank.py:66-68), ``torch``
 (CSR SpMV via ``index_add_`` + ``all_gather`` -- the NCCL baseline), ``fused`` (csrc/pagerank.cu: SpMV +
-damping + all-gather push in one launch per iteration).
+damping + all-gather push; the default warp layout runs ALL iterations of ``run(n)`` in one persistent
+cooperative launch, fp32 or fp64, contributions travelling by ``multimem.st`` when the heap has a multicast
+mapping).
 """
 from __future__ import annotations
 
@@ -53,16 +55,17 @@ class HubRows:
     chunk_start: torch.Tensor     # int64 [n_chunks] offsets into col
     chunk_end: torch.Tensor       # int64 [n_chunks]
     chunk_ptr: torch.Tensor       # int32 [n_hub + 1] chunks of hub row i
-    partial: torch.Tensor         # float32 [n_chunks] scratch
+    partial: torch.Tensor         # float64-sized scratch [n_chunks] (viewed as the run's value type)
     ptr: Optional[torch.Tensor] = None   # int64 [n_hub + 1] offsets of the hub rows in col
+    chunk_row: Optional[torch.Tensor] = None   # int32 [n_chunks] hub row index of each chunk
+    row_done: Optional[torch.Tensor] = None    # int32 [n_hub] completion counters (zero between iterations)
 
-    def c_struct(self) -> "_native.DapbPrHub":
-        h = _native.DapbPrHub()
+    def fill(self, h: "_native.DapbPrHub"):
         h.hub_rows, h.hub_col = self.rows.data_ptr(), self.col.data_ptr()
         h.chunk_start, h.chunk_end = self.chunk_start.data_ptr(), self.chunk_end.data_ptr()
         h.hub_chunk_ptr, h.chunk_partial = self.chunk_ptr.data_ptr(), self.partial.data_ptr()
         h.n_hub, h.n_chunks = int(self.rows.numel()), int(self.chunk_start.numel())
-        return h
+        h.chunk_row, h.row_done = self.chunk_row.data_ptr(), self.row_done.data_ptr()
 
 
 def split_hub_rows(row_ptr: torch.Tensor, col_idx: torch.Tensor, threshold: int, chunk: int = 2048):
@@ -75,7 +78,8 @@ def split_hub_rows(row_ptr: torch.Tensor, col_idx: torch.Tensor, threshold: int,
     if rows.numel() == 0:
         z = torch.zeros(0, dtype=i64, device=dev)
         return row_ptr, col_idx, HubRows(z.to(i32), z.to(i32), z, z, torch.zeros(1, dtype=i32, device=dev),
-                                         torch.zeros(0, dtype=torch.float32, device=dev), torch.zeros(1, dtype=i64, device=dev))
+                                         torch.zeros(1, dtype=torch.float64, device=dev), torch.zeros(1, dtype=i64, device=dev),
+                                         z.to(i32), torch.zeros(1, dtype=i32, device=dev))
     hs, he = row_ptr[rows], row_ptr[rows + 1]
     is_hub = torch.zeros(lens.numel(), dtype=torch.bool, device=dev)
     is_hub[rows] = True
@@ -98,25 +102,35 @@ def split_hub_rows(row_ptr: torch.Tensor, col_idx: torch.Tensor, threshold: int,
     c_start = hub_ptr[owner] + within * chunk
     c_end = torch.minimum(c_start + chunk, hub_ptr[owner + 1])
     hub = HubRows(rows.to(i32).contiguous(), hub_col, c_start.contiguous(), c_end.contiguous(),
-                  chunk_ptr.to(i32).contiguous(), torch.zeros(owner.numel(), dtype=torch.float32, device=dev), hub_ptr)
+                  chunk_ptr.to(i32).contiguous(), torch.zeros(owner.numel(), dtype=torch.float64, device=dev), hub_ptr,
+                  owner.to(i32).contiguous(), torch.zeros(rows.numel(), dtype=i32, device=dev))
     return rp, main_col, hub
 
 
 def balanced_vertex_bounds(indeg_all: torch.Tensor, world: int, vertex_cost: Optional[float] = None,
-                           hub_threshold: int = 64, hub_edge_cost: Optional[float] = None):
+                           hub_threshold: int = 64, hub_edge_cost: Optional[float] = None,
+                           outdeg_all: Optional[torch.Tensor] = None, push_cost: Optional[float] = None):
     """Contiguous destination-vertex ranges of (almost) equal modelled cost per rank.  A vertex costs 1, plus
-    ``vertex_cost`` if it has in-edges (row bookkeeping + its new contribution is pushed to every peer each iteration),
-    plus 1 per in-edge -- ``hub_edge_cost`` per in-edge for hub rows (> hub_threshold in-edges), whose non-zeros are
-    streamed by the cheaper chunk kernel.  R-MAT graphs concentrate edges on low vertex ids, so equal-size ranges would
-    give rank 0 most of the work.  ``DAPB_PR_VERTEX_COST`` / ``DAPB_PR_HUB_EDGE_COST`` override."""
+    ``vertex_cost`` if it has in-edges (row bookkeeping), plus 1 per in-edge -- ``hub_edge_cost`` per in-edge for hub
+    rows (> hub_threshold in-edges), whose non-zeros are streamed by the cheaper chunk path -- plus ``push_cost`` if it
+    has in-edges AND out-edges: only those vertices ever hold a non-zero contribution, so only they are pushed over
+    NVLink every iteration (pass ``outdeg_all`` to enable; the caller scales ``push_cost`` by the number of copies a
+    push makes: 1 with NVLS multicast, world - 1 with unicast stores).  R-MAT graphs concentrate edges on low vertex
+    ids, so equal-size ranges would give rank 0 most of the work and the last rank most of the vertices
+    (SURVEY.md 7.3-6).  ``DAPB_PR_VERTEX_COST`` / ``DAPB_PR_HUB_EDGE_COST`` / ``DAPB_PR_PUSH_COST`` override."""
     if vertex_cost is None:
         vertex_cost = float(os.environ.get("DAPB_PR_VERTEX_COST", 8))
     if hub_edge_cost is None:
         hub_edge_cost = float(os.environ.get("DAPB_PR_HUB_EDGE_COST", 1.0))
+    if push_cost is None:
+        push_cost = float(os.environ.get("DAPB_PR_PUSH_COST", 2.0))
     V = indeg_all.numel()
     deg = indeg_all.to(torch.float64)
     edge = torch.where(indeg_all > hub_threshold, deg * hub_edge_cost, deg)
-    cost = torch.cumsum(edge + vertex_cost * (indeg_all > 0) + 1, 0)
+    per_vertex = edge + vertex_cost * (indeg_all > 0) + 1
+    if outdeg_all is not None and push_cost > 0:
+        per_vertex = per_vertex + push_cost * ((indeg_all > 0) & (outdeg_all > 0))
+    cost = torch.cumsum(per_vertex, 0)
     total = float(cost[-1].item())
     targets = torch.tensor([total * r / world for r in range(1, world)], device=indeg_all.device, dtype=cost.dtype)
     cuts = torch.searchsorted(cost, targets, right=False).tolist() if world > 1 else []
@@ -128,9 +142,11 @@ def balanced_vertex_bounds(indeg_all: torch.Tensor, world: int, vertex_cost: Opt
 
 def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Optional[Dist] = None,
                         block_nnz: Optional[int] = None, balance: bool = True, layout: Optional[str] = None,
-                        hub_threshold: Optional[int] = None, hub_chunk: Optional[int] = None) -> ShardedGraph:
+                        hub_threshold: Optional[int] = None, hub_chunk: Optional[int] = None,
+                        push_copies: Optional[int] = None) -> ShardedGraph:
     """De-duplicate (ref pagerank.py:41) and build this rank's CSR(A^T) rows.  ``src``/``dst`` hold the FULL
-    edge list on every rank (the generators are deterministic), int64 on the target device."""
+    edge list on every rank (the generators are deterministic), int64 on the target device.  ``push_copies``: NVLink
+    copies one pushed contribution costs (1 = multicast, world - 1 = unicast) for the partitioner's egress term."""
     dist = dist or current()
     if layout is None:                  # "warp": warp-granular kernel + hub rows (default); "cta": CTA-wide row blocks
         layout = os.environ.get("DAPB_PR_LAYOUT", "warp")
@@ -147,8 +163,11 @@ def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Opti
     outdeg = torch.bincount(s_all, minlength=V)
     n_sources = int((outdeg > 0).sum().item())
     if balance and dist.world > 1:
+        copies = 1 if (push_copies is None or push_copies <= 0) else push_copies
         bounds = balanced_vertex_bounds(torch.bincount(d_all, minlength=V), dist.world,
-                                        hub_threshold=hub_threshold if layout == "warp" else (1 << 62))
+                                        hub_threshold=hub_threshold if layout == "warp" else (1 << 62),
+                                        outdeg_all=outdeg,
+                                        push_cost=float(os.environ.get("DAPB_PR_PUSH_COST", 2.0)) * copies)
     else:
         bounds = tuple(vertex_range(V, r, dist.world)[0] for r in range(dist.world)) + (V,)
     v0, v1 = bounds[dist.rank], bounds[dist.rank + 1]
@@ -182,28 +201,37 @@ def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Opti
 
 
 class ShardedPageRank:
-    """Iterates PageRank on a :class:`ShardedGraph`; ``ranks_local`` holds the owned slice."""
+    """Iterates PageRank on a :class:`ShardedGraph`; ``ranks_local`` holds the owned slice.
+
+    ``run(n)`` performs ``n`` iterations; with the fused backend and the warp layout that is ONE persistent cooperative
+    launch (csrc/pagerank.cu::pagerank_run_kernel), ``step()`` is ``run(1)``.  ``dtype`` float32 or float64 is honoured
+    by every backend (the CTA layout of the fused backend is float32 only)."""
 
     def __init__(self, graph: ShardedGraph, cfg: PageRankConfig, dist: Optional[Dist] = None,
-                 backend: str = "fused", heap=None, grid: int = 0, dtype=torch.float32):
+                 backend: str = "fused", heap=None, grid: int = 0, dtype=torch.float32, collect_stats: bool = False):
         self.g, self.cfg, self.backend = graph, cfg, backend
-        self.dtype = torch.float32 if backend == "fused" else dtype
         self.dist = dist or current()
+        if backend == "fused" and graph.hub is None and dtype != torch.float32:
+            raise ValueError("the CTA-layout fused kernel is float32 only; use layout='warp' for float64")
+        self.dtype = dtype
         dev = graph.row_ptr.device
         self.nv = graph.v1 - graph.v0
-        self.ranks_local = torch.zeros(self.nv, dtype=torch.float32, device=dev)
+        self.ranks_local = torch.zeros(self.nv, dtype=self.dtype, device=dev)
         self.n = max(graph.n_sources, 1)
         self.grid = grid
         self.it = 0
-        import os
         self.skip_empty = os.environ.get("DAPB_PR_NOSKIP") is None
+        self.stats = None
+        self._collect_stats = collect_stats
         if backend == "fused":
             from ..parallel.symm import default_heap
             self.lib = _native.load()
-            self.heap = heap or default_heap(max(1 << 30, 2 * graph.V * 4 + (64 << 20)))
-            self.region = self.heap.region(f"pagerank_V{graph.V}", 2 * graph.V * 4, _native.MAX_RANKS)
-            self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)
-            self._hub = graph.hub.c_struct() if graph.hub is not None else None
+            esz = 8 if dtype == torch.float64 else 4
+            self.heap = heap or default_heap(max(1 << 30, 2 * graph.V * esz + (64 << 20)))
+            self.region = self.heap.region(f"pagerank_V{graph.V}_b{esz}", 2 * graph.V * esz, _native.MAX_RANKS)
+            self.sync = torch.zeros(4, dtype=torch.int32, device=dev)
+            # float: 1/outdeg (multiply); double: outdeg itself (the kernel divides exactly like pagerank.py:24)
+            self.inv_outdeg = graph.inv_outdeg if dtype == torch.float32 else graph.outdeg_local.to(torch.float64).contiguous()
         else:
             self.c = None
         self.reset()
@@ -211,23 +239,27 @@ class ShardedPageRank:
     def reset(self):
         g = self.g
         self.it = 0
-        self._skip_from = 2               # rows without in-edges may be skipped once both parities hold their zeros
+        self._restored_at = 0             # iteration at which both parities were last rebuilt (init or restore)
         r0 = 1.0 / self.n
         if self.backend == "fused":
             if self.region.epoch % 2:
                 self.region.epoch += 1            # init writes parity 0 == (epoch_of_first_step - 1) & 1
             torch.cuda.synchronize()
             self.dist.barrier()
-            _native.check(self.lib.dapb_pagerank_init(self.heap.comm_ref(), g.inv_outdeg.data_ptr(), self.nv, g.v0, g.V,
-                                                      r0, self.region.payload_off, _native.stream_ptr()), "pagerank_init")
+            _native.check(self.lib.dapb_pagerank_init(self.heap.comm_ref(), self.inv_outdeg.data_ptr(), self.nv, g.v0, g.V,
+                                                      r0, self.region.payload_off, int(self.dtype == torch.float64),
+                                                      _native.stream_ptr()), "pagerank_init")
+            if g.hub is not None and g.hub.row_done is not None:
+                g.hub.row_done.zero_()
             torch.cuda.synchronize()
             self.dist.barrier()
             self._first = True
+            io = self.inv_outdeg
         else:
             self.inv = torch.where(g.outdeg_local > 0, 1.0 / g.outdeg_local.clamp(min=1).to(self.dtype),
                                    torch.zeros((), dtype=self.dtype, device=g.row_ptr.device))
             self.c = self._gather(r0 * self.inv)
-        io = g.inv_outdeg.to(self.dtype)
+            io = self.inv
         self.ranks_local = torch.where(io > 0, torch.full_like(io, r0), torch.zeros_like(io))
 
     def state_dict(self) -> dict:
@@ -244,13 +276,21 @@ class ShardedPageRank:
         dev = self.ranks_local.device
         self.ranks_local = torch.as_tensor(np.asarray(st["ranks_local"]), dtype=self.ranks_local.dtype, device=dev)
         self.it = int(st["it"])
-        self._skip_from = self.it + 2
+        self._restored_at = self.it
         if self.backend == "fused":
             self.finish()
             if self.region.epoch % 2:
                 self.region.epoch += 1
-            c = self._gather(self.ranks_local.float() * self.g.inv_outdeg)
-            self.heap.tensor(self.region, (2, self.g.V), torch.float32)[0].copy_(c)     # parity read by the next step
+            if self.dtype == torch.float32:         # same arithmetic as the kernel: r * (1/outdeg) in fp32, r / outdeg in fp64
+                c_loc = self.ranks_local * self.g.inv_outdeg
+            else:
+                deg = self.g.outdeg_local.to(self.dtype)
+                c_loc = torch.where(deg > 0, self.ranks_local / deg.clamp(min=1), torch.zeros_like(deg))
+            c = self._gather(c_loc)
+            buf = self.heap.tensor(self.region, (2, self.g.V), self.dtype)
+            buf[0].copy_(c)                     # parity read by the next step
+            # the other parity must read 0 wherever nothing is pushed any more (sinks, rows without in-edges)
+            buf[1].zero_()
             self._first = True
             self.finish()
         else:
@@ -267,29 +307,53 @@ class ShardedPageRank:
         return torch.cat([p[:b - a] for p, (a, b) in zip(parts, sizes)])
 
     def step(self):
-        with span("pagerank.step"):
-            self._step()
-        self.it += 1
+        self.run(1)
+
+    def run(self, n_iters: int):
+        """``n_iters`` more iterations (ref pagerank.py:50-57)."""
+        if n_iters <= 0:
+            return
+        with span("pagerank.run"):
+            if self.backend == "fused" and self.g.hub is not None:
+                self._run_persistent(n_iters)
+                self.it += n_iters
+            else:
+                for _ in range(n_iters):
+                    self._step()
+                    self.it += 1
+
+    def _run_persistent(self, n_iters: int):
+        g, cfg = self.g, self.cfg
+        a = _native.DapbPrRunArgs()
+        a.row_ptr, a.col_idx, a.inv_outdeg = g.row_ptr.data_ptr(), g.col_idx.data_ptr(), self.inv_outdeg.data_ptr()
+        a.blocks, a.n_blocks, a.f64 = g.blocks.data_ptr(), g.blocks.numel() - 1, int(self.dtype == torch.float64)
+        a.nv_local, a.v0, a.V = self.nv, g.v0, g.V
+        a.base, a.damp = cfg.q / self.n, 1.0 - cfg.q
+        a.ranks_local, a.c_off, a.flag_base = self.ranks_local.data_ptr(), self.region.payload_off, self.region.flag_base
+        a.epoch0 = self.region.epoch + 1
+        self.region.epoch += n_iters
+        # after a restore the zero rows of the read parity are rebuilt, so the same "third iteration" rule applies
+        a.n_iters, a.it0 = n_iters, self.it - self._restored_at
+        a.wait_first, a.skip_empty_ok, a.grid = 0 if self._first else 1, int(self.skip_empty), self.grid
+        a.sync = self.sync.data_ptr()
+        if self._collect_stats:
+            self.stats = torch.zeros(n_iters, 4, dtype=torch.int64, device=self.sync.device)
+            a.stats = self.stats.data_ptr()
+        g.hub.fill(a.hub)
+        _native.check(self.lib.dapb_pagerank_run(C.byref(a), self.heap.comm_ref(), _native.stream_ptr()), "pagerank_run")
+        self._first = False
 
     def _step(self):
         g, cfg = self.g, self.cfg
         base, damp = cfg.q / self.n, 1.0 - cfg.q
-        if self.backend == "fused":
-            wait_prev, skip = 0 if self._first else 1, int(self.it >= self._skip_from and self.skip_empty)
-            if g.hub is not None:               # warp-granular kernel + hub rows (csrc/pagerank.cu)
-                _native.check(self.lib.dapb_pagerank_step_v2(
-                    self.heap.comm_ref(), g.row_ptr.data_ptr(), g.col_idx.data_ptr(), g.inv_outdeg.data_ptr(),
-                    g.blocks.data_ptr(), g.blocks.numel() - 1, self.nv, g.v0, g.V, C.byref(self._hub),
-                    base, damp, self.ranks_local.data_ptr(), self.region.payload_off, self.region.flag_base,
-                    self.region.next_epoch(), self.ticket.data_ptr(), wait_prev, skip, self.grid,
-                    _native.stream_ptr()), "pagerank_step_v2")
-            else:
-                _native.check(self.lib.dapb_pagerank_step(
-                    self.heap.comm_ref(), g.row_ptr.data_ptr(), g.col_idx.data_ptr(), g.inv_outdeg.data_ptr(),
-                    g.blocks.data_ptr(), g.blocks.numel() - 1, self.nv, g.v0, g.V,
-                    base, damp, self.ranks_local.data_ptr(), self.region.payload_off, self.region.flag_base,
-                    self.region.next_epoch(), self.ticket.data_ptr(), wait_prev, skip, self.grid,
-                    _native.stream_ptr()), "pagerank_step")
+        if self.backend == "fused":             # CTA layout: one launch per iteration
+            wait_prev, skip = 0 if self._first else 1, int(self.it - self._restored_at >= 2 and self.skip_empty)
+            _native.check(self.lib.dapb_pagerank_step(
+                self.heap.comm_ref(), g.row_ptr.data_ptr(), g.col_idx.data_ptr(), g.inv_outdeg.data_ptr(),
+                g.blocks.data_ptr(), g.blocks.numel() - 1, self.nv, g.v0, g.V,
+                base, damp, self.ranks_local.data_ptr(), self.region.payload_off, self.region.flag_base,
+                self.region.next_epoch(), self.sync.data_ptr(), wait_prev, skip, self.grid,
+                _native.stream_ptr()), "pagerank_step")
             self._first = False
         else:
             vals = self.c[g.col_idx.long()]
@@ -303,6 +367,21 @@ class ShardedPageRank:
             r = torch.where(s > 0, base + damp * s, torch.zeros_like(s))
             self.ranks_local = r
             self.c = self._gather(r * self.inv)
+
+    def push_bytes_per_iter(self) -> int:
+        """NVLink egress of this rank per iteration: vertices with in- AND out-edges x value size x copies."""
+        g = self.g
+        lens = g.row_ptr[1:] - g.row_ptr[:-1]
+        has_in = lens > 0
+        if g.hub is not None and g.hub.rows.numel():
+            has_in = has_in.clone()
+            has_in[g.hub.rows.long()] = True
+        n_push = int((has_in & (g.outdeg_local > 0)).sum().item())
+        esz = 8 if self.dtype == torch.float64 else 4
+        if self.dist.world == 1 or self.backend != "fused":
+            return 0
+        copies = 1 if self.heap.multicast else self.dist.world - 1
+        return n_push * esz * copies
 
     def finish(self):
         """Make sure every rank's last pushes landed before buffers are reused (fused backend)."""
@@ -334,6 +413,7 @@ def run_pagerank(edges: Iterable[Tuple[int, int]], cfg: PageRankConfig, backend:
     dst = torch.tensor([remap[b] for _, b in edges], dtype=torch.int64, device=dist.device)
     g = build_sharded_graph(src, dst, len(ids), dist)
     pr = ShardedPageRank(g, cfg, dist, backend="fused" if backend == "fused" else "nccl", dtype=torch.float64)
+    every = checkpoint_every if (path_wanted := checkpoint is not None) and checkpoint_every > 0 else 0
     path = None if checkpoint is None else ck.rank_path(checkpoint, dist.rank)
     meta = dict(kind="pagerank", V=len(ids), n_edges=int(g.n_edges), world=int(dist.world))
     if path and resume:
@@ -343,8 +423,9 @@ def run_pagerank(edges: Iterable[Tuple[int, int]], cfg: PageRankConfig, backend:
             ck.check_meta(m, **meta)
             pr.load_state_dict(st)
     while pr.it < cfg.n_iterations:
-        pr.step()
-        if path and checkpoint_every > 0 and (pr.it % checkpoint_every == 0 or pr.it == cfg.n_iterations):
+        left = cfg.n_iterations - pr.it
+        pr.run(min(left, every - pr.it % every) if every else left)      # one persistent launch per checkpoint interval
+        if path and every and (pr.it % every == 0 or pr.it == cfg.n_iterations):
             ck.save_checkpoint(path, pr.state_dict(), dict(meta, iteration=pr.it))
     r = pr.ranks().double().cpu().numpy()
     return {ids[i]: float(r[i]) for i in range(len(ids)) if r[i] > 0}

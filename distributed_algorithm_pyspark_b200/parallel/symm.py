@@ -1,14 +1,24 @@
 """Symmetric heap over NVLink peer memory (host side of csrc/comm.cuh).
 
-Each rank ``cudaMalloc``s one heap (flags in the first 64 KiB, payload after), the CUDA IPC
-handles are exchanged once through ``torch.distributed`` (bootstrap only) and every peer heap is
-mapped into every process.  Kernels then push data straight into peer memory; NCCL is not on any
-hot path.  Regions are handed out by a bump allocator that every rank drives identically, so an
-offset means the same thing everywhere ("symmetric").
+Each rank owns one heap (flags in the first 64 KiB, payload after) that every peer has mapped; kernels push
+data straight into peer memory and NCCL is not on any hot path.  Regions are handed out by a bump allocator
+that every rank drives identically, so an offset means the same thing everywhere ("symmetric").
+
+Two ways of getting the mappings (``DAPB_HEAP_BACKEND=auto|vmm|ipc``):
+
+* ``vmm`` -- the heap is a ``cuMemCreate`` allocation made and exchanged through
+  ``torch.distributed._symmetric_memory`` (fd passing, peer mappings).  When the fabric supports it the
+  allocation is also bound to an NVLS **multicast** object and ``comm.mc_heap`` carries that mapping: one
+  ``multimem.st`` then reaches all ranks and ``multimem.ld_reduce`` sums in the switch (csrc/comm.cuh).
+* ``ipc`` -- plain ``cudaMalloc`` + ``cudaIpc*`` handles exchanged through ``all_gather_object``; unicast only
+  (every primitive keeps a pure P2P path).
+
+``auto`` tries ``vmm`` and falls back to ``ipc`` (the decision is agreed on by all ranks).
 """
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import Dict, Optional
 
@@ -37,14 +47,64 @@ class SymmetricHeap:
         self.dist = dist or current()
         self.lib = _native.load()
         self.nbytes = int(nbytes)
-        base = C.c_void_p()
-        _native.check(self.lib.dapb_symm_alloc(self.nbytes, C.byref(base)), "symm_alloc")
-        self.base = base.value
-        self._peer_ptrs = [None] * self.dist.world
-        self._peer_ptrs[self.dist.rank] = self.base
         self._payload_top = 0
         self._flag_top = 0
         self._regions: Dict[str, Region] = {}
+        self._peer_ptrs = [None] * self.dist.world
+        self.mc_ptr = 0
+        self._vmm = None                    # (tensor, handle) keep-alive of the torch symmetric-memory allocation
+        want = os.environ.get("DAPB_HEAP_BACKEND", "auto")
+        if self.dist.world > 1 and want in ("auto", "vmm"):
+            self._try_vmm(required=(want == "vmm"))
+        self.backend = "vmm" if self._vmm is not None else "ipc"
+        if self._vmm is None:
+            self._init_ipc()
+        self.comm = _native.DapbComm()
+        self.comm.rank = self.dist.rank
+        self.comm.world = self.dist.world
+        self.comm.heap_bytes = self.nbytes
+        for r in range(self.dist.world):
+            self.comm.heap[r] = self._peer_ptrs[r]
+        use_mc = os.environ.get("DAPB_MULTICAST", "1") != "0"
+        self.comm.mc_heap = self.mc_ptr if (self.mc_ptr and use_mc) else None
+
+    @property
+    def multicast(self) -> bool:
+        return bool(self.comm.mc_heap)
+
+    def _try_vmm(self, required: bool):
+        """cuMemCreate-backed heap with peer + multicast mappings via torch's symmetric-memory rendezvous."""
+        import torch.distributed as tdist
+        err = None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            t = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=self.dist.device)
+            hdl = symm_mem.rendezvous(t, tdist.group.WORLD)
+            t.zero_()
+            torch.cuda.synchronize()
+            ptrs = [int(p) for p in hdl.buffer_ptrs]
+            if len(ptrs) != self.dist.world or ptrs[self.dist.rank] != t.data_ptr():
+                raise RuntimeError("unexpected symmetric-memory pointer table")
+            mc = int(hdl.multicast_ptr or 0)
+        except Exception as e:                  # noqa: BLE001 -- any failure means "use the IPC heap"
+            err = repr(e)[:200]
+        oks = self.dist.all_gather_object(err is None)
+        if not all(oks):
+            if required:
+                raise RuntimeError(f"DAPB_HEAP_BACKEND=vmm but the symmetric-memory rendezvous failed: {err}")
+            return
+        self._vmm = (t, hdl)
+        self.base = ptrs[self.dist.rank]
+        self._peer_ptrs = ptrs
+        mcs = self.dist.all_gather_object(mc != 0)
+        self.mc_ptr = mc if all(mcs) else 0
+        self.dist.barrier()
+
+    def _init_ipc(self):
+        base = C.c_void_p()
+        _native.check(self.lib.dapb_symm_alloc(self.nbytes, C.byref(base)), "symm_alloc")
+        self.base = base.value
+        self._peer_ptrs[self.dist.rank] = self.base
         if self.dist.world > 1:
             handle = (C.c_ubyte * 64)()
             _native.check(self.lib.dapb_ipc_get_handle(self.base, handle), "ipc_get_handle")
@@ -57,12 +117,6 @@ class SymmetricHeap:
                 _native.check(self.lib.dapb_ipc_open_handle(buf, C.byref(out)), f"ipc_open_handle(rank {r})")
                 self._peer_ptrs[r] = out.value
             self.dist.barrier()
-        self.comm = _native.DapbComm()
-        self.comm.rank = self.dist.rank
-        self.comm.world = self.dist.world
-        self.comm.heap_bytes = self.nbytes
-        for r in range(self.dist.world):
-            self.comm.heap[r] = self._peer_ptrs[r]
 
     # ------------------------------------------------------------------ allocation
     def region(self, name: str, nbytes: int, n_flags: int) -> Region:
@@ -105,6 +159,11 @@ class SymmetricHeap:
         if self.base is None:
             return
         torch.cuda.synchronize()
+        if self._vmm is not None:
+            self.dist.barrier()
+            self._vmm = None                # torch unmaps and releases the allocation with the last reference
+            self.base = None
+            return
         if self.dist.world > 1:
             self.dist.barrier()
             for r, p in enumerate(self._peer_ptrs):

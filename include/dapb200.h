@@ -28,12 +28,16 @@ extern "C" {
 #define DAPB_ERR_UNSUPPORTED (-2)
 
 /* Symmetric-heap view handed to kernels that communicate (csrc/comm.cuh).
- * heap[r] = base of rank r's heap as mapped into THIS process; heap[rank] is local memory. */
+ * heap[r] = base of rank r's heap as mapped into THIS process; heap[rank] is local memory.
+ * mc_heap = NVLS multicast mapping of the same heap (a store to mc_heap + x lands at heap[r] + x on EVERY rank, a
+ * multimem.ld_reduce from it sums the W copies inside the NVSwitch), or NULL when the fabric offers no multicast --
+ * every kernel then falls back to W unicast peer stores / loads. */
 typedef struct DapbComm {
   int32_t rank;
   int32_t world;
   void* heap[DAPB_MAX_RANKS];
   uint64_t heap_bytes;
+  void* mc_heap;
 } DapbComm;
 
 /* ------------------------------------------------------------------ runtime ------------ */
@@ -51,13 +55,33 @@ DAPB_API int dapb_ipc_close_handle(void* ptr);
  * out_fail (device int32) receives the number of mismatching elements. */
 DAPB_API int dapb_comm_selftest(void* heaps, uint64_t heap_bytes, int32_t world, int32_t n, int32_t iters,
                        int32_t* out_fail, void* stream);
+/* Cross-GPU stress of the flag protocol: one persistent CTA per rank runs `iters` consecutive one-shot all-reduces of n
+ * floats (epochs epoch0 .. epoch0+iters-1) with random in-kernel stalls and checks every result bit for bit;
+ * out_fail (device int32, zero it first) receives the number of wrong elements. */
+DAPB_API int dapb_allreduce_stress(const DapbComm* comm, uint64_t payload_off, uint32_t flag_base, uint64_t epoch0,
+                                   int32_t n, int32_t iters, uint32_t seed, int32_t* out_fail, void* stream);
 /* Stand-alone F8 collectives (tests / baselines; production kernels inline them).
- * One CTA per rank; every rank must call with the same epoch (strictly increasing per flag_base). */
+ * One CTA per rank; every rank must call with the same epoch, which must grow by EXACTLY 1 per call on a
+ * flag_base (payload slots are double-buffered on the epoch's parity, so skipping an epoch would let a fast
+ * rank overwrite a slot a slower peer still reads). */
 DAPB_API int dapb_allreduce_f32(const DapbComm* comm, uint64_t payload_off, uint32_t flag_base,
                        uint64_t epoch, const float* src, float* dst, int32_t n, void* stream);
 DAPB_API int dapb_allreduce_f64(const DapbComm* comm, uint64_t payload_off, uint32_t flag_base,
                        uint64_t epoch, const double* src, double* dst, int32_t n, void* stream);
 DAPB_API int dapb_barrier(const DapbComm* comm, uint32_t flag_base, uint64_t epoch, void* stream);
+/* Grid-wide stand-alone collectives for large messages (cooperative launches; multimem.* when comm->mc_heap is set,
+ * unicast peer loads/stores otherwise).  Each call uses `world` flag words at flag_base and TWO barrier epochs
+ * (2*epoch-1, 2*epoch); `epoch` must grow by exactly 1 per call on a flag_base.  Payload at payload_off:
+ * all-gather world*n_per_rank elements, two-shot / reduce-scatter n floats (n % (4*world) == 0), all-to-all
+ * world*n_per_pair u64.  Replaces: collect / reduceByKey shuffles / join shuffles. */
+DAPB_API int dapb_allgather(const DapbComm* comm, uint64_t payload_off, uint32_t flag_base, uint64_t epoch,
+                            const void* src, void* dst, int64_t n_per_rank, int32_t elem_bytes, void* stream);
+DAPB_API int dapb_allreduce_twoshot_f32(const DapbComm* comm, uint64_t payload_off, uint32_t flag_base, uint64_t epoch,
+                                        const float* src, float* dst, int32_t n, void* stream);
+DAPB_API int dapb_reduce_scatter_f32(const DapbComm* comm, uint64_t payload_off, uint32_t flag_base, uint64_t epoch,
+                                     const float* src, float* dst /* [n / world] */, int32_t n, void* stream);
+DAPB_API int dapb_alltoall_u64(const DapbComm* comm, uint64_t payload_off, uint32_t flag_base, uint64_t epoch,
+                               const unsigned long long* src, unsigned long long* dst, int64_t n_per_pair, void* stream);
 
 /* ------------------------------------------------------------------ F1/F2 logistic -------
  * ref: optimization/ssgd.py:23-33,93-112; machine_learning/logistic_regression.py:76-92;
@@ -134,6 +158,10 @@ DAPB_API int dapb_lr_step(const DapbLrStepArgs* args, const DapbComm* comm, void
 /* Tensor-core variant (tcgen05.mma forward K-major + backward MN-major, TMEM accumulators, hi/lo bf16 split of w
  * and of the residual): bf16 rows, D == 1024, grid defaults to one CTA per SM (partials must hold `grid` rows). */
 DAPB_API int dapb_lr_step_tc(const DapbLrStepArgs* args, const DapbComm* comm, void* stream);
+/* out[i] = 1 iff row row_base+i is in the mini-batch of `iteration` (same Philox rule as the step kernels).  Serves the
+ * PyTorch+NCCL baseline, which must train on the identical batches (ref ssgd.py:97 `sample(False, f, 42 + t)`). */
+DAPB_API int dapb_philox_mask(int64_t row_base, int64_t n_rows, uint64_t seed, uint32_t iteration, uint32_t threshold24,
+                              uint8_t* out, void* stream);
 /* Test-set accuracy with the reference's 0.5 threshold (ref ssgd.py:107-110). acc_out: [1] float. */
 DAPB_API int dapb_lr_eval(const void* X, const float* y, int64_t n_rows, int32_t D, int32_t dtype,
                  const float* w, float eps, float* acc_out, uint32_t* scratch2, void* stream);
@@ -189,12 +217,13 @@ DAPB_API int dapb_kmeans_assign_tc_dbg(const void* X, int64_t n, int32_t d, cons
                                        int32_t* counts, int32_t grid, long long* dbg, void* stream);
 
 /* ------------------------------------------------------------------ F4 PageRank -----------
- * ref: graph_computation/pagerank.py:21-25,44-57.  Contribution vector [2][V] float lives in the
+ * ref: graph_computation/pagerank.py:21-25,44-57.  Contribution vector [2][V] lives in the
  * symmetric heap at c_off; iteration `epoch` reads parity (epoch-1)&1 and pushes into parity epoch&1
  * on every rank.  Host must barrier between dapb_pagerank_init and the first step (wait_prev = 0).
- * skip_empty = 1 (allowed from the 3rd step after init) skips rows without in-edges: both buffers already hold 0. */
-DAPB_API int dapb_pagerank_init(const DapbComm* comm, const float* inv_outdeg, int64_t nv_local, int64_t v0,
-                                int64_t V, float r0, uint64_t c_off, void* stream);
+ * skip_empty = 1 (allowed from the 3rd step after init) skips rows without in-edges: both buffers already hold 0.
+ * dapb_pagerank_step is the simple CTA-per-row-block kernel (one launch per iteration, float only). */
+DAPB_API int dapb_pagerank_init(const DapbComm* comm, const void* inv_outdeg, int64_t nv_local, int64_t v0,
+                                int64_t V, double r0, uint64_t c_off, int32_t f64, void* stream);
 DAPB_API int dapb_pagerank_step(const DapbComm* comm, const int64_t* row_ptr, const int32_t* col_idx,
                                 const float* inv_outdeg, const int32_t* blocks, int32_t n_blocks,
                                 int64_t nv_local, int64_t v0, int64_t V, float base,
@@ -202,24 +231,43 @@ DAPB_API int dapb_pagerank_step(const DapbComm* comm, const int64_t* row_ptr, co
                                 uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t skip_empty,
                                 int32_t grid, void* stream);
 
-/* Warp-granular variant: one warp per row block of <= 512 (non-zeros + rows); rows longer than the host's hub
- * threshold are removed from the main CSR (length 0 there) and described here: their non-zeros live in hub_col, cut
- * into chunks [chunk_start, chunk_end) that belong to hub rows hub_chunk_ptr[i] .. hub_chunk_ptr[i+1]. */
+/* Persistent warp-granular PageRank: n_iters iterations in ONE cooperative launch; between iterations the ranks
+ * synchronise through flag words in the heap, contributions travel by multimem.st (or unicast peer stores).
+ * One warp per row block of <= 512 (non-zeros + rows); rows longer than the host's hub threshold are removed from
+ * the main CSR (length 0 there) and described by DapbPrHub: their non-zeros live in hub_col, cut into chunks
+ * [chunk_start, chunk_end) that belong to hub rows hub_chunk_ptr[i] .. hub_chunk_ptr[i+1].
+ * Values (inv_outdeg, ranks_local, chunk_partial, the [2][V] contribution vector at c_off) are float, or double when
+ * f64 = 1 (parity with the 17-digit ranks the reference prints, ref pagerank.py:60-68).  With f64 = 1 `inv_outdeg`
+ * holds the out-degree ITSELF (the kernel divides, like the reference) and no multiply-add is contracted. */
 typedef struct DapbPrHub {
   const int32_t* hub_rows;      /* [n_hub] local row ids, ascending */
   const int32_t* hub_col;       /* non-zeros (source ids) of all hub rows, row after row */
   const int64_t* chunk_start;   /* [n_chunks] offsets into hub_col */
   const int64_t* chunk_end;     /* [n_chunks] */
   const int32_t* hub_chunk_ptr; /* [n_hub + 1] */
-  float* chunk_partial;         /* [n_chunks] scratch */
+  void* chunk_partial;          /* [n_chunks] scratch (value type) */
   int32_t n_hub, n_chunks;
+  const int32_t* chunk_row;     /* [n_chunks] hub row index of each chunk */
+  uint32_t* row_done;           /* [n_hub] scratch, zero before first use */
 } DapbPrHub;
-DAPB_API int dapb_pagerank_step_v2(const DapbComm* comm, const int64_t* row_ptr, const int32_t* col_idx,
-                                   const float* inv_outdeg, const int32_t* blocks, int32_t n_blocks,
-                                   int64_t nv_local, int64_t v0, int64_t V, const DapbPrHub* hub, float base,
-                                   float damp, float* ranks_local, uint64_t c_off, uint32_t flag_base,
-                                   uint64_t epoch, uint32_t* ticket, int32_t wait_prev, int32_t skip_empty,
-                                   int32_t grid, void* stream);
+typedef struct DapbPrRunArgs {
+  const int64_t* row_ptr; const int32_t* col_idx; const void* inv_outdeg; const int32_t* blocks;
+  int32_t n_blocks, f64;
+  int64_t nv_local, v0, V;
+  double base, damp;            /* q/n and 1-q */
+  void* ranks_local;            /* [nv_local] out */
+  uint64_t c_off;               /* payload offset of the contribution vector */
+  uint32_t flag_base;           /* `world` flags */
+  uint64_t epoch0;              /* epoch of the first iteration (>= 1; grows by 1 per iteration, also across launches) */
+  int32_t n_iters, it0;         /* it0: iterations done since dapb_pagerank_init */
+  int32_t wait_first;           /* 0 right after init + host barrier, else 1 */
+  int32_t skip_empty_ok;        /* 1: rows without in-edges are skipped from the third iteration after init */
+  int32_t grid;                 /* 0 = as many CTAs as can be co-resident */
+  uint32_t* sync;               /* [4] scratch */
+  unsigned long long* stats;    /* optional [n_iters][4] %globaltimer stamps (enter, wait passed, last ticket, published) */
+  DapbPrHub hub;
+} DapbPrRunArgs;
+DAPB_API int dapb_pagerank_run(const DapbPrRunArgs* args, const DapbComm* comm, void* stream);
 
 /* ------------------------------------------------------------------ F6 transitive closure --
  * ref: graph_computation/transitive_closure.py:27-40.  Pairs are packed (x << 32 | z); the hash set

@@ -38,6 +38,51 @@ def main():
         want = sum(r + 1 + it for r in range(dist.world))
         ok = ok and bool((dst == want).all().item())
     out["allreduce_ok"] = ok
+    out["heap_backend"], out["multicast"] = heap.backend, bool(heap.multicast)
+    # ---- flag-protocol stress on real peers: 100k epochs in one persistent launch per rank, random stalls, bitwise check
+    fail = torch.zeros(1, dtype=torch.int32, device=dev)
+    iters = 100_000
+    _native.check(lib.dapb_allreduce_stress(heap.comm_ref(), reg.payload_off, reg.flag_base, reg.epoch + 1, 1024, iters,
+                                            17, fail.data_ptr(), _native.stream_ptr()))
+    reg.epoch += iters
+    torch.cuda.synchronize()
+    out["stress_fail"] = int(fail.item())
+    # ---- grid-wide collectives (multimem.* when the heap is multicast-mapped) against torch.distributed
+    import torch.distributed as tdist
+    W = dist.world
+    big = heap.region("coll_test", 8 << 20, 8)
+    coll_ok = {}
+    for rep in range(3):
+        n = 4096 * W * (rep + 1)
+        x = torch.randn(n, device=dev, generator=torch.Generator(device=dev).manual_seed(100 * rep + dist.rank))
+        want = x.clone()
+        tdist.all_reduce(want)
+        got = torch.empty_like(x)
+        _native.check(lib.dapb_allreduce_twoshot_f32(heap.comm_ref(), big.payload_off, big.flag_base, big.next_epoch(),
+                                                     x.data_ptr(), got.data_ptr(), n, _native.stream_ptr()))
+        gs = dist.all_gather(got)
+        coll_ok[f"twoshot{rep}"] = bool(torch.allclose(got, want, rtol=1e-5, atol=1e-5)) and all(torch.equal(gs[0], t) for t in gs)
+        rs_got = torch.empty(n // W, device=dev)
+        _native.check(lib.dapb_reduce_scatter_f32(heap.comm_ref(), big.payload_off, big.flag_base, big.next_epoch(),
+                                                  x.data_ptr(), rs_got.data_ptr(), n, _native.stream_ptr()))
+        coll_ok[f"rs{rep}"] = bool(torch.allclose(rs_got, want[dist.rank * (n // W):(dist.rank + 1) * (n // W)], rtol=1e-5, atol=1e-5))
+        for dt, eb in ((torch.float32, 4), (torch.float64, 8)):
+            m = 1000 * (rep + 1) + 3
+            xs = torch.randn(m, device=dev, dtype=dt) + dist.rank
+            ag = torch.empty(m * W, device=dev, dtype=dt)
+            _native.check(lib.dapb_allgather(heap.comm_ref(), big.payload_off, big.flag_base, big.next_epoch(),
+                                             xs.data_ptr(), ag.data_ptr(), m, eb, _native.stream_ptr()))
+            coll_ok[f"ag{rep}_{eb}"] = bool(torch.equal(ag, torch.cat(dist.all_gather(xs))))
+        m = 500 * (rep + 1)
+        snd = torch.arange(W * m, device=dev, dtype=torch.int64) + 1_000_000 * dist.rank
+        rcv = torch.empty_like(snd)
+        _native.check(lib.dapb_alltoall_u64(heap.comm_ref(), big.payload_off, big.flag_base, big.next_epoch(),
+                                            snd.data_ptr(), rcv.data_ptr(), m, _native.stream_ptr()))
+        want_rcv = torch.cat([torch.arange(dist.rank * m, (dist.rank + 1) * m, device=dev, dtype=torch.int64) + 1_000_000 * r
+                              for r in range(W)])
+        coll_ok[f"a2a{rep}"] = bool(torch.equal(rcv, want_rcv))
+    torch.cuda.synchronize()
+    out["collectives"] = coll_ok
     # ---- logistic engines: fused vs nccl, identical Philox masks
     torch.manual_seed(100 + dist.rank)
     n, D = 20000, 256
@@ -82,6 +127,25 @@ def main():
         pb.step()
     ra, rb = pa.ranks(), pb.ranks()
     out["pagerank_rel_diff"] = float(((ra - rb).abs() / (rb.abs() + 1e-12)).max().item())
+    # persistent launch (all 10 iterations in one kernel), hub rows, fp32 and fp64; must equal the stepped run bit for bit
+    g2 = build_sharded_graph(src, dst, 1 << 12, dist, hub_threshold=32, hub_chunk=128)
+    out["pagerank_run"] = {}
+    for dt in (torch.float32, torch.float64):
+        p1 = ShardedPageRank(g2, cfg, dist, backend="fused", heap=heap, dtype=dt, collect_stats=True)
+        p1.run(10)
+        r1 = p1.ranks().clone()
+        p2 = ShardedPageRank(g2, cfg, dist, backend="fused", heap=heap, dtype=dt)
+        for _ in range(10):
+            p2.step()
+        r2 = p2.ranks()
+        p3 = ShardedPageRank(g2, cfg, dist, backend="nccl", dtype=torch.float64)
+        p3.run(10)
+        r3 = p3.ranks()
+        out["pagerank_run"][str(dt)] = {
+            "run_equals_steps": bool(torch.equal(r1, r2)),
+            "rel_diff_vs_fp64": float(((r1.double() - r3).abs() / r3.clamp(min=1e-300))[r3 > 0].max().item()),
+            "same_support": bool(torch.equal(r1 > 0, r3 > 0)),
+            "push_bytes_per_iter": p1.push_bytes_per_iter()}
     # ---- transitive closure of a supercritical graph: buffers must grow mid-run on every rank (persistent kernel:
     #      status GROW decided from the in-kernel message matrix, no host collective), three drivers must agree
     from distributed_algorithm_pyspark_b200.models.transitive_closure import closure_device

@@ -69,6 +69,11 @@ def test_reference_scripts_fused_multi_gpu(tmp_path, breast_cancer):
 def test_engines_fused_vs_nccl_multi_gpu(tmp_path):
     out = _torchrun("_engine_worker.py", tmp_path / "e.json", _nproc(), 29712)
     assert out["allreduce_ok"]
+    assert out["stress_fail"] == 0                              # 100k epochs of the flag protocol on real peers
+    assert all(out["collectives"].values()), out["collectives"]
+    for dt, r in out["pagerank_run"].items():
+        assert r["run_equals_steps"] and r["same_support"], (dt, r)
+        assert r["rel_diff_vs_fp64"] < (1e-4 if "32" in dt else 1e-12), (dt, r)
     for algo, r in out["lr"].items():
         assert r["rel_diff"] < 5e-3, (algo, r)
         assert r["bit_identical_across_ranks"], algo
