@@ -256,94 +256,191 @@ __device__ __forceinline__ float reg_grad_f(float w, int reg_type, float a) {
   return 0.f;
 }
 
-// Finalize: executed by the LAST CTA of the grid once every CTA's partial is in `partials`.
-// g_s: shared scratch of >= D + 4 floats.
-__device__ void lr_finalize(const DapbLrStepArgs& a, const DapbComm& c, float* g_s) {
-  const int D = a.D, tid = threadIdx.x;
+// ---------------------------------------------------------------------------------------------------------------
+// Grid finish, slice-parallel: the LAST kFinSlices CTAs to arrive each take one column slice of the model and run, for
+// that slice only: the deterministic sum of the G partial rows -> the in-kernel all-reduce over NVLink peers -> the
+// optimiser update.  (One CTA doing all of it was a 40-50 us serial tail per step: 1.2 MB of partials through one SM,
+// then one all-reduce; eight slices shrink both eight-fold and run their eight small all-reduces concurrently.)
+//   * election: every CTA takes a ticket after publishing its partial row; tickets >= G - S are finalizers, slice =
+//     ticket - (G - S).  A finalizer spins until the ticket reaches G (all rows published; the stragglers it waits for
+//     are running or schedulable because at most S CTAs ever spin).
+//   * every finalizer sums the G counts itself (the update of each slice needs the global batch size).
+//   * finalizers bump the ticket once more when done; the one that brings it to G + S resets it for the next launch.
+//   * programmatic dependent launch: finalizers let the NEXT step kernel start (griddepcontrol.launch_dependents);
+//     that kernel samples and L2-prefetches its first rows, then blocks in griddepcontrol.wait until this grid has
+//     completed and flushed, i.e. until the new w is visible.
+// Payload per slice: 2 (parity) x world x (cps + 4) floats at payload_off + slice * that; flags flag_base + slice*world + r.
+// sm: shared scratch of >= 5 * blockDim.x + cps + 8 floats.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kFinSlices = 8;
+__host__ __device__ __forceinline__ int lr_cols_per_slice(int D) { return (((D + kFinSlices - 1) / kFinSlices) + 3) & ~3; }
+
+__device__ __forceinline__ unsigned ld_acquire_gpu_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+__device__ void lr_finish_slice(const DapbLrStepArgs& a, const DapbComm& c, float* sm, int slice) {
+  const int D = a.D, tid = threadIdx.x, nt = blockDim.x;
   const int G = gridDim.x;
-  // deterministic sum over CTAs in blockIdx order
-  for (int d0 = tid * 4; d0 < D; d0 += blockDim.x * 4) {
-    if (d0 + 4 <= D && (D & 3) == 0) {
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
-      for (int b = 0; b < G; ++b) {
-        float4 v = __ldcg(reinterpret_cast<const float4*>(a.partials + (int64_t)b * D + d0));
-        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+  const int cps = lr_cols_per_slice(D);
+  const int c0 = min(D, slice * cps), c1 = min(D, c0 + cps), nc = c1 - c0;
+  float* g_s = sm;                         // [cps + 4]: slice of the gradient, then the count in two 16-bit halves
+  float* red = sm + cps + 8;               // [nt * 4] cross-row-group scratch
+  __shared__ int s_cnt_local;
+  unsigned long long t0 = 0;
+  if (a.stats && slice == 0 && tid == 0) t0 = global_timer_ns();
+
+  // ---- deterministic sum of the G partial rows over this slice's columns (fixed thread layout, fixed order) ----
+  const bool vec = (D & 3) == 0 && ((reinterpret_cast<uintptr_t>(a.partials) & 15) == 0);
+  const int unit = vec ? 4 : 1;
+  const int nvec = nc / unit;              // nc is a multiple of 4 whenever vec (cps and D are)
+  for (int v0 = 0; v0 < nvec; v0 += 32) {
+    const int cw = min(32, nvec - v0);     // vectors handled in this pass
+    const int RG = nt / cw;                // row groups
+    const int rg = tid / cw, cv = tid - rg * cw;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (rg < RG) {
+      const int col = c0 + (v0 + cv) * unit;
+      if (vec) {
+#pragma unroll 8
+        for (int b = rg; b < G; b += RG) {
+          const float4 v = __ldcg(reinterpret_cast<const float4*>(a.partials + (int64_t)b * D + col));
+          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+      } else {
+#pragma unroll 8
+        for (int b = rg; b < G; b += RG) acc.x += __ldcg(a.partials + (int64_t)b * D + col);
       }
-      g_s[d0] = acc.x; g_s[d0 + 1] = acc.y; g_s[d0 + 2] = acc.z; g_s[d0 + 3] = acc.w;
-    } else {
-      for (int d = d0; d < min(d0 + 4, D); ++d) {
-        float acc = 0.f;
-        for (int b = 0; b < G; ++b) acc += __ldcg(a.partials + (int64_t)b * D + d);
-        g_s[d] = acc;
-      }
+      reinterpret_cast<float4*>(red)[rg * cw + cv] = acc;
     }
+    __syncthreads();
+    if (tid < cw) {
+      float4 t = reinterpret_cast<float4*>(red)[tid];
+      for (int r = 1; r < RG; ++r) {
+        const float4 v = reinterpret_cast<float4*>(red)[r * cw + tid];
+        t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+      }
+      const int o = (v0 + tid) * unit;
+      g_s[o] = t.x;
+      if (vec) { g_s[o + 1] = t.y; g_s[o + 2] = t.z; g_s[o + 3] = t.w; }
+    }
+    __syncthreads();
   }
-  if (tid == 0) {
+  if (tid < 32) {                          // batch size of this rank (every slice needs it)
     int cnt = 0;
-    for (int b = 0; b < G; ++b) cnt += __ldcg(a.counts + b);
-    g_s[D] = (float)cnt;          // exact for counts < 2^24; larger counts go through g_s[D+1..]
-    g_s[D + 1] = __int_as_float(cnt);
+    for (int b = tid; b < G; b += 32) cnt += __ldcg(a.counts + b);
+    cnt = warp_sum(cnt);
+    if (tid == 0) s_cnt_local = cnt;
   }
   __syncthreads();
-  int cnt_local = __float_as_int(g_s[D + 1]);
+  const int cnt_local = s_cnt_local;
+  if (a.stats && slice == 0 && tid == 0) { a.stats[0] = t0; a.stats[1] = global_timer_ns(); }
+
+  const uint64_t off = a.payload_off + (uint64_t)slice * 2 * c.world * (cps + 4) * sizeof(float);
+  const uint32_t fb = a.flag_base + (uint32_t)slice * c.world;
 
   if (a.fin == DAPB_LR_FIN_GRAD_ONLY) {
-    for (int d = tid; d < D; d += blockDim.x) a.g_out[d] = g_s[d];
-    if (tid == 0 && a.cnt_out) *a.cnt_out = cnt_local;
+    for (int d = tid; d < nc; d += nt) a.g_out[c0 + d] = g_s[d];
+    if (slice == 0 && tid == 0) {
+      if (a.cnt_out) *a.cnt_out = cnt_local;
+      if (a.cnt_accum) *a.cnt_accum += (unsigned long long)cnt_local;
+    }
     return;
   }
 
   if (a.fin == DAPB_LR_FIN_SSGD) {
-    // all-reduce [g | cnt(int bits in 2 halves)] : counts are summed exactly as two 16-bit halves in fp32
+    // all-reduce [g slice | cnt in two 16-bit halves]: the halves are summed exactly in fp32
     if (tid == 0) {
-      g_s[D] = (float)(cnt_local & 0xffff);
-      g_s[D + 1] = (float)(cnt_local >> 16);
+      g_s[nc] = (float)(cnt_local & 0xffff);
+      g_s[nc + 1] = (float)(cnt_local >> 16);
     }
     __syncthreads();
-    block_allreduce_oneshot<float>(c, c.rank, a.payload_off, a.flag_base, a.epoch, g_s, g_s, D + 2);
-    const int cnt_i = (int)g_s[D] + ((int)g_s[D + 1] << 16);
+    block_allreduce_oneshot<float>(c, c.rank, off, fb, a.epoch, g_s, g_s, nc + 2);
+    if (a.stats && slice == 0 && tid == 0) a.stats[2] = global_timer_ns();
+    const int cnt_i = (int)g_s[nc] + ((int)g_s[nc + 1] << 16);
     const float cnt_tot = (float)cnt_i;
-    for (int d = tid; d < D; d += blockDim.x) {
-      float wd = a.w[d], g = g_s[d];
-      if (a.g_out) a.g_out[d] = g;
+    for (int d = tid; d < nc; d += nt) {
+      float wd = a.w[c0 + d], g = g_s[d];
+      if (a.g_out) a.g_out[c0 + d] = g;
       if (a.use_sum) wd -= a.eta * g;                                         // ref logistic_regression.py:85
       else if (cnt_tot > 0.f) wd -= a.eta * (g / cnt_tot + a.lam * reg_grad_f(wd, a.reg_type, a.reg_alpha));
-      a.w[d] = wd;                                                            // ref ssgd.py:105
+      a.w[c0 + d] = wd;                                                       // ref ssgd.py:105
     }
-    if (tid == 0 && a.cnt_out) *a.cnt_out = cnt_i;
+    if (slice == 0 && tid == 0) {
+      if (a.cnt_out) *a.cnt_out = cnt_i;
+      if (a.cnt_accum) *a.cnt_accum += (unsigned long long)cnt_i;
+      if (a.stats) a.stats[3] = global_timer_ns();
+    }
     return;
   }
 
   // LOCAL / LOCAL_SYNC : replica step  (ref ma.py:42-43, easgd.py:45)
-  for (int d = tid; d < D; d += blockDim.x) {
-    float wl = a.w_local[d];
+  for (int d = tid; d < nc; d += nt) {
+    float wl = a.w_local[c0 + d];
     if (cnt_local > 0) {
       float nv = wl - a.eta * (g_s[d] / (float)cnt_local);
-      if (a.algo == DAPB_LR_EASGD) nv -= a.alpha * (wl - a.w[d]);
+      if (a.algo == DAPB_LR_EASGD) nv -= a.alpha * (wl - a.w[c0 + d]);
       wl = nv;
     }
     g_s[d] = wl;
-    if (a.fin == DAPB_LR_FIN_LOCAL) a.w_local[d] = wl;
+    if (a.fin == DAPB_LR_FIN_LOCAL) a.w_local[c0 + d] = wl;
   }
-  if (tid == 0 && a.cnt_out) *a.cnt_out = cnt_local;
+  if (slice == 0 && tid == 0) {
+    if (a.cnt_out) *a.cnt_out = cnt_local;
+    if (a.cnt_accum) *a.cnt_accum += (unsigned long long)cnt_local;
+  }
   if (a.fin == DAPB_LR_FIN_LOCAL) return;
   __syncthreads();
   // model all-reduce fused with the MA average / BMUF filter / EASGD centre update
   // (ref ma.py:104-106, bmuf.py:109-114, easgd.py:104-106)
-  float* sum_s = g_s + ((D + 7) & ~3);
-  block_allreduce_oneshot<float>(c, c.rank, a.payload_off, a.flag_base, a.epoch, g_s, sum_s, D);
+  float* sum_s = red;                      // nt * 4 >= cps floats for every supported block size
+  block_allreduce_oneshot<float>(c, c.rank, off, fb, a.epoch, g_s, sum_s, nc);
+  if (a.stats && slice == 0 && tid == 0) a.stats[2] = global_timer_ns();
   const float invP = 1.f / (float)a.n_replicas_total;
-  for (int d = tid; d < D; d += blockDim.x) {
-    float S = sum_s[d], wd = a.w[d];
+  for (int d = tid; d < nc; d += nt) {
+    float S = sum_s[d], wd = a.w[c0 + d];
     if (a.algo == DAPB_LR_MA) wd = S * invP;
     else if (a.algo == DAPB_LR_BMUF) {
-      float nd = a.mu * a.delta_w[d] + a.zeta * (S * invP - wd);
-      a.delta_w[d] = nd;
+      float nd = a.mu * a.delta_w[c0 + d] + a.zeta * (S * invP - wd);
+      a.delta_w[c0 + d] = nd;
       wd += nd;
     } else wd = (1.f - a.beta) * wd + a.beta * S * invP;
-    a.w[d] = wd;
-    a.w_local[d] = a.reset_replica ? wd : g_s[d];
+    a.w[c0 + d] = wd;
+    a.w_local[c0 + d] = a.reset_replica ? wd : g_s[d];
+  }
+  if (a.stats && slice == 0 && tid == 0) a.stats[3] = global_timer_ns();
+}
+
+// CTA-collective tail of every step kernel: publish order is partial row -> __threadfence -> ticket.
+__device__ void lr_grid_finish(const DapbLrStepArgs& a, const DapbComm& c, float* sm) {
+  __shared__ unsigned s_ticket;
+  const unsigned G = gridDim.x;
+  const unsigned S = G < (unsigned)kFinSlices ? G : (unsigned)kFinSlices;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_ticket = atomicAdd(a.ticket, 1u);
+  __syncthreads();
+  const unsigned ticket = s_ticket;
+  if (ticket + S < G) return;                          // not one of the last S arrivals
+  pdl_launch_dependents();
+  if (threadIdx.x == 0) {
+    unsigned spins = 0;
+    while (ld_acquire_gpu_u32(a.ticket) < G) if (++spins > 64) __nanosleep(40);
+  }
+  __syncthreads();
+  // slices beyond S (G < kFinSlices) are folded onto the last finalizer
+  const int first = (int)(ticket - (G - S));
+  if (S == (unsigned)kFinSlices) lr_finish_slice(a, c, sm, first);
+  else for (int sl = first; sl < kFinSlices; sl += (int)S) { lr_finish_slice(a, c, sm, sl); __syncthreads(); }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned t = atomicAdd(a.ticket, 1u);
+    if (t == G + S - 1) *a.ticket = 0;                 // ready for the next launch
   }
 }
 
@@ -360,7 +457,6 @@ __global__ void __launch_bounds__(kStepThreads, 2) lr_step_kernel(DapbLrStepArgs
   constexpr int D = 32 * EPL;
   extern __shared__ __align__(16) float smem[];   // [D (weights) | max(kStepWarps*D, 2*D+32)]
   __shared__ int s_cnt;
-  __shared__ bool s_last;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 
   // forward weights in shared memory, permuted to this kernel's lane order so that every lane
@@ -368,16 +464,11 @@ __global__ void __launch_bounds__(kStepThreads, 2) lr_step_kernel(DapbLrStepArgs
   constexpr int kQ = kE / 4;
   float4* w4 = reinterpret_cast<float4*>(smem);
   float* red = smem + D;                               // [kStepWarps][D] reduction scratch
-  for (int i = tid; i < D / 4; i += kStepThreads) {
-    const int ln = i & 31, jq = i >> 5, j = jq / kQ, q = jq % kQ;
-    w4[i] = *reinterpret_cast<const float4*>(a.w_fwd + (j * 32 + ln) * kE + 4 * q);
-  }
   float acc[EPL];
 #pragma unroll
   for (int i = 0; i < EPL; ++i) acc[i] = 0.f;
   int kept = 0;
   if (tid == 0) s_cnt = 0;
-  __syncthreads();
 
   const int64_t n_chunks = (a.n_rows + 31) >> 5;
   const int64_t warp_g = (int64_t)blockIdx.x * kStepWarps + wid;
@@ -403,6 +494,15 @@ __global__ void __launch_bounds__(kStepThreads, 2) lr_step_kernel(DapbLrStepArgs
       asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(pn), "r"((uint32_t)(D * sizeof(T))) : "memory");
     }
   }
+  // Everything above (sampling decisions, L2 prefetch of the first rows) is independent of the model; from here on
+  // the previous step's w is needed: with programmatic dependent launch this kernel may have started while the previous
+  // step's finalizers were still exchanging gradients -- wait until that grid has completed and its writes are visible.
+  pdl_wait();
+  for (int i = tid; i < D / 4; i += kStepThreads) {
+    const int ln = i & 31, jq = i >> 5, j = jq / kQ, q = jq % kQ;
+    w4[i] = *reinterpret_cast<const float4*>(a.w_fwd + (j * 32 + ln) * kE + 4 * q);
+  }
+  __syncthreads();
   for (int64_t ch = warp_g; ch < n_chunks; ch += warp_n) {
     bool keep;
     if (PF > 0) {
@@ -487,18 +587,7 @@ __global__ void __launch_bounds__(kStepThreads, 2) lr_step_kernel(DapbLrStepArgs
     a.partials[(int64_t)blockIdx.x * D + d] = s;
   }
   if (tid == 0) a.counts[blockIdx.x] = s_cnt;
-  // ---- last-CTA election -------------------------------------------------------------------------
-  __threadfence();
-  __syncthreads();
-  if (tid == 0) {
-    unsigned t = atomicAdd(a.ticket, 1u);
-    s_last = (t == gridDim.x - 1);
-    if (s_last) *a.ticket = 0;                         // ready for the next launch
-  }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  lr_finalize(a, c, red);
+  lr_grid_finish(a, c, red);
 }
 
 // Generic path (any D <= 8192): per-warp accumulators in shared memory.
@@ -506,8 +595,8 @@ template <typename T>
 __global__ void __launch_bounds__(kStepThreads) lr_step_generic_kernel(DapbLrStepArgs a, DapbComm c) {
   extern __shared__ __align__(16) float smem[];       // [kStepWarps][D] (+ finalize scratch)
   __shared__ int s_cnt;
-  __shared__ bool s_last;
   const int D = a.D, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  pdl_wait();
   float* acc = smem + (int64_t)wid * D;
   for (int d = lane; d < D; d += 32) acc[d] = 0.f;
   if (tid == 0) s_cnt = 0;
@@ -537,30 +626,39 @@ __global__ void __launch_bounds__(kStepThreads) lr_step_generic_kernel(DapbLrSte
     a.partials[(int64_t)blockIdx.x * D + d] = s;
   }
   if (tid == 0) a.counts[blockIdx.x] = s_cnt;
-  __threadfence();
-  __syncthreads();
-  if (tid == 0) {
-    unsigned t = atomicAdd(a.ticket, 1u);
-    s_last = (t == gridDim.x - 1);
-    if (s_last) *a.ticket = 0;
-  }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  lr_finalize(a, c, smem);
+  lr_grid_finish(a, c, smem);
 }
+
+// Launch with programmatic stream serialization: a step kernel queued behind another step kernel may begin (sample,
+// prefetch) as soon as the earlier grid's finalizers signal griddepcontrol.launch_dependents.  DAPB_LR_PDL=0 disables.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t s, Args... args) {
+  static const bool use_pdl = !(getenv("DAPB_LR_PDL") && atoi(getenv("DAPB_LR_PDL")) == 0);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = use_pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
+// shared-memory floats the grid finish needs behind the kernel's own scratch pointer (see lr_finish_slice)
+inline size_t lr_finish_floats(int D, int threads) { return (size_t)lr_cols_per_slice(D) + 8 + 4 * (size_t)threads + 16; }
 
 template <typename T, int EPL>
 int launch_fast(const DapbLrStepArgs& a, const DapbComm& c, int grid, cudaStream_t s) {
   constexpr int D = 32 * EPL;
-  size_t smem = sizeof(float) * (size_t)(D + (kStepWarps * D > 2 * D + 32 ? kStepWarps * D : 2 * D + 32));
+  size_t red = kStepWarps * D > 2 * D + 32 ? kStepWarps * D : 2 * D + 32;
+  if (red < lr_finish_floats(D, kStepThreads)) red = lr_finish_floats(D, kStepThreads);
+  size_t smem = sizeof(float) * (size_t)(D + red);
   // prefetch distance: 16-bit rows 1 chunk ahead by default, 32-bit rows none (measured); DAPB_LR_PREFETCH=0|1|2 overrides
   static const int pf_env = getenv("DAPB_LR_PREFETCH") ? atoi(getenv("DAPB_LR_PREFETCH")) : -1;
   const int pf = pf_env >= 0 ? pf_env : (sizeof(T) == 2 ? 1 : 0);
 #define DAPB_LAUNCH_PF(N)                                                                                              \
   {                                                                                                                     \
     DAPB_CUDA_CHECK(cudaFuncSetAttribute(lr_step_kernel<T, EPL, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    lr_step_kernel<T, EPL, N><<<grid, kStepThreads, smem, s>>>(a, c);                                                   \
+    DAPB_CUDA_CHECK(launch_pdl(lr_step_kernel<T, EPL, N>, grid, kStepThreads, smem, s, a, c));                          \
   }
   if (pf >= 2) DAPB_LAUNCH_PF(2) else if (pf == 1) DAPB_LAUNCH_PF(1) else DAPB_LAUNCH_PF(0)
 #undef DAPB_LAUNCH_PF
@@ -569,15 +667,21 @@ int launch_fast(const DapbLrStepArgs& a, const DapbComm& c, int grid, cudaStream
 }
 template <typename T>
 int launch_generic(const DapbLrStepArgs& a, const DapbComm& c, int grid, cudaStream_t s) {
-  size_t smem = sizeof(float) * (size_t)(kStepWarps * a.D > 2 * a.D + 32 ? kStepWarps * a.D : 2 * a.D + 32);
+  size_t fl = kStepWarps * a.D > 2 * a.D + 32 ? kStepWarps * a.D : 2 * a.D + 32;
+  if (fl < lr_finish_floats(a.D, kStepThreads)) fl = lr_finish_floats(a.D, kStepThreads);
+  size_t smem = sizeof(float) * fl;
   DAPB_REQUIRE(smem <= 220 * 1024, "lr_step: D=%d too large for the generic kernel", a.D);
   DAPB_CUDA_CHECK(cudaFuncSetAttribute(lr_step_generic_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  lr_step_generic_kernel<T><<<grid, kStepThreads, smem, s>>>(a, c);
+  DAPB_CUDA_CHECK(launch_pdl(lr_step_generic_kernel<T>, grid, kStepThreads, smem, s, a, c));
   DAPB_LAUNCH_CHECK();
   return 0;
 }
 
 }  // namespace
+
+extern "C" uint64_t dapb_lr_step_payload_bytes(int32_t world, int32_t D) {
+  return (uint64_t)kFinSlices * 2 * world * (lr_cols_per_slice(D) + 4) * sizeof(float);
+}
 
 extern "C" int dapb_lr_step(const DapbLrStepArgs* args, const DapbComm* comm, void* stream) {
   DAPB_REQUIRE(args && comm, "lr_step: null argument");
@@ -591,14 +695,17 @@ extern "C" int dapb_lr_step(const DapbLrStepArgs* args, const DapbComm* comm, vo
     DAPB_REQUIRE(c.world >= 1 && c.world <= DAPB_MAX_RANKS, "lr_step: bad world");
     DAPB_REQUIRE(a.epoch >= 1, "lr_step: epoch starts at 1");
     if (c.world > 1) {
-      uint64_t need = DAPB_FLAG_BYTES + a.payload_off + (uint64_t)2 * c.world * ((a.D + 2 + 3) & ~3) * sizeof(float);
+      uint64_t need = DAPB_FLAG_BYTES + a.payload_off + dapb_lr_step_payload_bytes(c.world, a.D);
       DAPB_REQUIRE(need <= c.heap_bytes, "lr_step: heap too small");
+      DAPB_REQUIRE((a.flag_base + (uint64_t)DAPB_LR_STEP_FLAGS) * 8 <= DAPB_FLAG_BYTES, "lr_step: flag range");
     }
   }
   int grid = a.grid > 0 ? a.grid : 2 * dapb::sm_count();
   a.grid = grid;
   cudaStream_t s = (cudaStream_t)stream;
-  const bool aligned = (reinterpret_cast<uintptr_t>(a.X) & 15) == 0;
+  // the fast kernels read X, w_fwd (float4) and the partial rows (float4) with 16-byte vector loads
+  const bool aligned = ((reinterpret_cast<uintptr_t>(a.X) | reinterpret_cast<uintptr_t>(a.w_fwd) |
+                         reinterpret_cast<uintptr_t>(a.partials)) & 15) == 0;
   if (aligned && a.dtype == 1) {
     switch (a.D) {
       case 256: return launch_fast<__nv_bfloat16, 8>(a, c, grid, s);
@@ -677,9 +784,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) lr_tc_kernel(DapbLrStepArgs a, 
   uint64_t* r_empty = r_full + 2;                   // [2] 1 (MMA commit)
   uint64_t* g_done = r_empty + 2;                   // 1
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(smem + kTcTmemOff);
-  __shared__ bool s_last;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
+  pdl_wait();                                        // the previous step's w must be visible (see lr_grid_finish)
 
   if (tid == 0) {
     for (int i = 0; i < kTcRing; ++i) { mbar_init(&slot_full[i], 8); mbar_init(&slot_empty[i], 1); }
@@ -919,15 +1026,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) lr_tc_kernel(DapbLrStepArgs a, 
   tc_fence_before();
   __syncthreads();
   if (warp == 2) tmem_dealloc(tmem_base, 256);
-  if (tid == 0) {
-    unsigned tk = atomicAdd(a.ticket, 1u);
-    s_last = (tk == gridDim.x - 1);
-    if (s_last) *a.ticket = 0;
-  }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  lr_finalize(a, c, reinterpret_cast<float*>(smem));
+  lr_grid_finish(a, c, reinterpret_cast<float*>(smem));
 }
 
 }  // namespace
@@ -944,14 +1043,14 @@ extern "C" int dapb_lr_step_tc(const DapbLrStepArgs* args, const DapbComm* comm,
   DAPB_REQUIRE(a.partials && a.counts && a.ticket && a.w_fwd, "lr_step_tc: missing scratch / weights");
   if ((a.fin == DAPB_LR_FIN_SSGD || a.fin == DAPB_LR_FIN_LOCAL_SYNC) && c.world > 1) {
     DAPB_REQUIRE(a.epoch >= 1, "lr_step_tc: epoch starts at 1");
-    uint64_t need = DAPB_FLAG_BYTES + a.payload_off + (uint64_t)2 * c.world * ((a.D + 2 + 3) & ~3) * sizeof(float);
+    uint64_t need = DAPB_FLAG_BYTES + a.payload_off + dapb_lr_step_payload_bytes(c.world, a.D);
     DAPB_REQUIRE(need <= c.heap_bytes, "lr_step_tc: heap too small");
   }
   int grid = a.grid > 0 ? a.grid : dapb::sm_count();
   a.grid = grid;
   const uint32_t smem = kTcTotal + 1024;
   DAPB_CUDA_CHECK(cudaFuncSetAttribute(lr_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  lr_tc_kernel<<<grid, kTcThreads, smem, (cudaStream_t)stream>>>(a, c, smem);
+  DAPB_CUDA_CHECK(launch_pdl(lr_tc_kernel, grid, kTcThreads, (size_t)smem, (cudaStream_t)stream, a, c, smem));
   DAPB_LAUNCH_CHECK();
   return 0;
 }

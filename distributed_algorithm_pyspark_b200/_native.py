@@ -70,9 +70,11 @@ class DapbLrStepArgs(C.Structure):
         ("g_out", C.c_void_p), ("cnt_out", C.c_void_p), ("w", C.c_void_p), ("w_local", C.c_void_p),
         ("delta_w", C.c_void_p), ("reset_replica", C.c_int32),
         ("payload_off", C.c_uint64), ("flag_base", C.c_uint32), ("epoch", C.c_uint64),
+        ("cnt_accum", C.c_void_p), ("stats", C.c_void_p),
     ]
 
 
+LR_STEP_FLAGS = 64
 ALGO_ID = {"ssgd": 0, "gd": 1, "ma": 2, "bmuf": 3, "easgd": 4}
 REG_ID = {"none": 0, "l2": 1, "l1": 2, "elastic_net": 3}
 FIN_GRAD_ONLY, FIN_SSGD, FIN_LOCAL, FIN_LOCAL_SYNC = 0, 1, 2, 3
@@ -106,6 +108,7 @@ def _declare(lib: C.CDLL):
         "dapb_alltoall_u64": (C.c_int, [P(DapbComm), u64, u32, u64, vp, vp, i64, vp]),
         "dapb_lr_parity_run": (C.c_int, [P(DapbLrParityArgs), P(DapbComm), vp]),
         "dapb_lr_parity_payload_bytes": (u64, [i32, i32]),
+        "dapb_lr_step_payload_bytes": (u64, [i32, i32]),
         "dapb_lr_step": (C.c_int, [P(DapbLrStepArgs), P(DapbComm), vp]),
         "dapb_lr_step_tc": (C.c_int, [P(DapbLrStepArgs), P(DapbComm), vp]),
         "dapb_philox_mask": (C.c_int, [i64, i64, u64, u32, u32, vp, vp]),

@@ -295,7 +295,7 @@ class ShardedLogisticEngine:
 
     def __init__(self, X: torch.Tensor, y: torch.Tensor, cfg: LogisticConfig, row_base: int = 0,
                  dist: Optional[Dist] = None, backend: str = "fused", w0: Optional[torch.Tensor] = None,
-                 grid: int = 0, heap=None, use_tc: bool = False):
+                 grid: int = 0, heap=None, use_tc: bool = False, collect_stats: bool = False):
         self.dist = dist or current()
         self.cfg, self.backend = cfg, backend
         assert X.dim() == 2 and X.is_contiguous() and X.dtype in _DTYPE_ID
@@ -325,7 +325,10 @@ class ShardedLogisticEngine:
             self.counts = torch.zeros(self.grid, dtype=torch.int32, device=dev)
             self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)
             self.g = torch.zeros(self.D, dtype=torch.float32, device=dev)
-            self.region = self.heap.region(f"lr_step_D{self.D}", 2 * _native.MAX_RANKS * (self.D + 8) * 4, _native.MAX_RANKS)
+            nbytes = int(self.lib.dapb_lr_step_payload_bytes(_native.MAX_RANKS, self.D))
+            self.region = self.heap.region(f"lr_step_D{self.D}", nbytes, _native.LR_STEP_FLAGS)
+            self.samples_seen = torch.zeros(1, dtype=torch.int64, device=dev)      # running sum of batch sizes (in-kernel)
+            self.stats = torch.zeros(4, dtype=torch.int64, device=dev) if collect_stats else None
             self._eval_scratch = torch.zeros(2, dtype=torch.int32, device=dev)
             self._acc = torch.zeros(1, dtype=torch.float32, device=dev)
             self._args = self._base_args()
@@ -345,6 +348,8 @@ class ShardedLogisticEngine:
         a.g_out, a.cnt_out = self.g.data_ptr(), self.last_count.data_ptr()
         a.w, a.w_local, a.delta_w = self.w.data_ptr(), self.w_local.data_ptr(), self.delta_w.data_ptr()
         a.payload_off, a.flag_base = self.region.payload_off, self.region.flag_base
+        a.cnt_accum = self.samples_seen.data_ptr()
+        a.stats = self.stats.data_ptr() if self.stats is not None else 0
         return a
 
     def _launch(self, fin: int, w_fwd: torch.Tensor, iteration: int, reset: int = 0, stream=None):

@@ -150,10 +150,19 @@ typedef struct DapbLrStepArgs {
   float* w_local;           /* [D] in/out replica (LOCAL / LOCAL_SYNC) */
   float* delta_w;           /* [D] in/out (BMUF) */
   int32_t reset_replica;    /* LOCAL_SYNC: copy new w into w_local (MA/BMUF, ref ma.py:96) */
-  uint64_t payload_off;     /* needs 2*world*(D+4) floats */
-  uint32_t flag_base;       /* needs `world` flags */
-  uint64_t epoch;           /* strictly increasing per call on this flag_base */
+  uint64_t payload_off;     /* needs dapb_lr_step_payload_bytes(world, D) */
+  uint32_t flag_base;       /* needs DAPB_LR_STEP_FLAGS flags (8 column slices x up to 8 ranks) */
+  uint64_t epoch;           /* +1 per call on this flag_base (SSGD / LOCAL_SYNC calls) */
+  unsigned long long* cnt_accum;  /* optional: += the step's batch size (global for SSGD, local otherwise) */
+  unsigned long long* stats;      /* optional [4] %globaltimer ns of slice 0: finish entered, partials reduced,
+                                     all-reduce done, update done */
 } DapbLrStepArgs;
+#define DAPB_LR_STEP_FLAGS 64
+DAPB_API uint64_t dapb_lr_step_payload_bytes(int32_t world, int32_t D);
+/* Alignment: X, w_fwd and partials 16-byte aligned select the vectorised kernels (D in {128,256,512,1024}); any other
+ * alignment (4-byte minimum) or D falls back to the generic kernel -- never a fault.
+ * Launched with programmatic stream serialization: back-to-back step kernels on one stream overlap the next step's
+ * sampling / L2 prefetch with this step's cross-GPU exchange (the kernel waits before it reads w). */
 DAPB_API int dapb_lr_step(const DapbLrStepArgs* args, const DapbComm* comm, void* stream);
 /* Tensor-core variant (tcgen05.mma forward K-major + backward MN-major, TMEM accumulators, hi/lo bf16 split of w
  * and of the residual): bf16 rows, D == 1024, grid defaults to one CTA per SM (partials must hold `grid` rows). */
@@ -176,7 +185,13 @@ DAPB_API int dapb_lr_eval(const void* X, const float* y, int64_t n_rows, int32_t
  * loading this library holds until exit.  Limits: 1 <= D <= DAPB_NOALLOC_MAX_D, otherwise DAPB_ERR_INVALID
  * with a message.  The first call on each device looks the array's address up (cudaGetSymbolAddress);
  * make that first call outside of any stream capture.  All calls share the array: calls that may overlap
- * on the GPU (other streams / threads) race -- serialise them. */
+ * on the GPU (other streams / threads) race -- serialise them.
+ * When the memory is actually taken: with CUDA's lazy module loading (the default) the array is backed when this
+ * library's logistic module is first used on a device -- the first call of this function or of any dapb_lr_* entry
+ * point -- not when the .so is loaded.  A host whose allocator is about to claim the rest of the GPU must therefore
+ * make that first call BEFORE it does so (or run with CUDA_MODULE_LOADING=EAGER); afterwards no call allocates.
+ * The scratch address is looked up for the CURRENT device: `stream`, X, y, w and the outputs must belong to it.
+ * X, w 16-byte aligned select the vectorised kernels; other alignments run the generic kernel (never a fault). */
 #define DAPB_NOALLOC_MAX_D 1024
 #define DAPB_NOALLOC_MAX_GRID 296
 DAPB_API int dapb_lr_grad_noalloc(const void* X, const float* y, int64_t n_rows, int64_t row_base, int32_t D,
