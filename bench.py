@@ -7,12 +7,23 @@ of mini-batch samples pushed through forward + backward + update per second (who
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|nccl|reference] [--no-extras]
 N > 1 is launched by ``python -m torch.distributed.run`` (RANK / LOCAL_RANK / WORLD_SIZE from the env).
+
+What one line carries besides the contract keys:
+  vs_baseline            value / the same metric of the in-box PyTorch + NCCL (+ cuBLAS) arm, run in this process on the same
+                         data, masks and N (``baseline`` holds its numbers).  The reference publishes no number
+                         (BASELINE.json "published": {}) and PySpark is not installable here, so this is the north star's
+                         comparative baseline.
+  sustained_ms_per_step  the same step replayed for >= 1 s, device-timed (the K-step burst is ~25-50 ms)
+  checks                 results asserted after the timed steps (weights bit-identical across ranks, ...)
+  extra                  the other BASELINE.json configs (EASGD / MA / BMUF, k-means x 20, PageRank scale-26 x 30, ...)
+                         each with its own ``*_vs_baseline``
 """
 import argparse
 import json
 import os
 import sys
 import time
+import zlib
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -32,11 +43,14 @@ def parse():
     ap.add_argument("--dim", type=int, default=1024)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--fraction", type=float, default=0.1)
-    ap.add_argument("--no-extras", action="store_true", help="only the headline metric and its e2e number")
+    ap.add_argument("--no-extras", action="store_true", help="only the headline metric, its baseline and its e2e number")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-baseline", action="store_true", help="skip the in-process PyTorch+NCCL arm (vs_baseline = null)")
+    ap.add_argument("--baseline-steps", type=int, default=5)
     ap.add_argument("--lr-kernel", default="auto", choices=["auto", "cuda", "tc"],
                     help="logistic step kernel: CUDA-core streaming kernel or the tcgen05 variant (auto = the faster one measured)")
     ap.add_argument("--e2e-steps", type=int, default=6)
+    ap.add_argument("--pagerank-scale", type=int, default=26)
     return ap.parse_args()
 
 
@@ -70,32 +84,50 @@ def timed_steps(dist, step_fn, steps, warmup, sampler=None):
     return dist.max_over_ranks(a.elapsed_time(b))
 
 
-def bench_logistic(args, dist, algo, steps, warmup, backend, X, y, sampler=None):
+def bench_logistic(args, dist, algo, steps, warmup, backend, X, y, sampler=None, keep_engine=False):
+    """Device-timed optimiser steps.  The number of samples is counted on the device: the fused kernels add every step's
+    batch size to ``engine.samples_seen`` themselves (nothing but step kernels sits in the stream, so consecutive
+    steps chain through programmatic dependent launch); the baseline accumulates ``last_count`` with a torch add."""
     import torch
     from distributed_algorithm_pyspark_b200.config import LogisticConfig
     from distributed_algorithm_pyspark_b200.models.logistic import ShardedLogisticEngine
     cfg = LogisticConfig.for_algo(algo, eta=0.1, mini_batch_fraction=args.fraction, seed=0, sampler="philox",
                                   n_slices=dist.world)
     eng = ShardedLogisticEngine(X, y, cfg, row_base=dist.rank * X.shape[0], dist=dist, backend=backend,
-                                use_tc=(args.lr_kernel == "tc"))
-    total = torch.zeros(1, dtype=torch.int64, device=X.device)
+                                use_tc=(args.lr_kernel == "tc"), collect_stats=(backend == "fused"))
+    n_inner = 1 if algo in ("ssgd", "gd", "easgd") else cfg.n_local_iterations
+    if backend == "fused":
+        step = eng.step
+        counter = eng.samples_seen
+    else:
+        counter = torch.zeros(1, dtype=torch.int64, device=X.device)
 
-    def step():
-        eng.step()
-        total.add_(eng.last_count)
-
+        def step():
+            eng.step()
+            counter.add_(eng.last_count)
     ms = timed_steps(dist, step, steps, warmup, sampler)
     torch.cuda.synchronize()
-    counted = int(total.item())
-    # ssgd reports the GLOBAL count per step; local-SGD modes report the local one
+    counted = int(counter.item())
+    # ssgd / gd count the GLOBAL batch once per step; the local-SGD modes count this rank's batch once per local step
+    # (fused) or once per round (baseline)
     if algo in ("ssgd", "gd"):
         samples = counted * steps / (steps + warmup)
     else:
-        samples = dist.sum_over_ranks(counted) * steps / (steps + warmup)
-        samples *= 1 if algo == "easgd" else cfg.n_local_iterations        # gradient evaluations
-    launches_per_step = 1 if algo in ("ssgd", "gd", "easgd") else cfg.n_local_iterations
-    return {"ms_per_step": ms / steps, "samples_per_s": samples / (ms / 1e3), "launches": launches_per_step * steps,
-            "engine": eng}
+        per_round = counted / ((steps + warmup) * (n_inner if backend == "fused" else 1))
+        samples = dist.sum_over_ranks(per_round) * steps * n_inner        # gradient evaluations of the whole job
+    out = {"ms_per_step": ms / steps, "samples_per_s": samples / (ms / 1e3), "launches": n_inner * steps}
+    if backend == "fused" and eng.stats is not None:
+        st = eng.stats.cpu().tolist()
+        mine = {"rank": dist.rank, "reduce_partials_us": (st[1] - st[0]) / 1e3, "exchange_us": (st[2] - st[1]) / 1e3,
+                "update_us": (st[3] - st[2]) / 1e3}
+        out["finish_breakdown_last_step"] = dist.all_gather_object(mine)
+    if keep_engine:
+        out["engine"] = eng
+    return out
+
+
+def crc_of(t) -> int:
+    return zlib.crc32(t.detach().cpu().numpy().tobytes())
 
 
 def bench_e2e_resident(args, dist, X, y, steps, warmup):
@@ -136,7 +168,9 @@ def bench_e2e_resident(args, dist, X, y, steps, warmup):
 
 def bench_e2e(args, dist, X, y, steps, warmup):
     """Same metric end to end through the public streaming API: every step's mini-batch is copied from pinned
-    host memory and the step's result (test accuracy + batch size) is read back to the host."""
+    host memory and the step's result (test accuracy + batch size) is read back to the host.  Also measures the
+    box's host->device ceiling with all ranks copying at once (plain pinned cudaMemcpyAsync of the same buffer), so the
+    achieved H2D rate can be read against what the PCIe / host-memory path delivers at this N."""
     import torch
     from distributed_algorithm_pyspark_b200.config import LogisticConfig
     from distributed_algorithm_pyspark_b200.models.logistic import StreamingLogisticEngine
@@ -175,10 +209,25 @@ def bench_e2e(args, dist, X, y, steps, warmup):
     wall = time.perf_counter() - t0
     ms = dist.max_over_ranks(max(a.elapsed_time(b), wall * 1e3))
     samples = sum(c for _, c in results)            # global counts
-    return {"value": samples / (ms / 1e3), "unit": "samples/s", "h2d_bytes_per_step": eng.h2d_bytes // steps,
-            "d2h_bytes_per_step": eng.d2h_bytes // steps, "ms_per_step": ms / steps, "steps": steps,
-            "batch_rows_per_gpu": rows, "last_acc": results[-1][0] if results else None,
-            "api": "StreamingLogisticEngine.fit_stream (pinned host batches, double-buffered H2D, per-step D2H of accuracy+count)"}
+    h2d = eng.h2d_bytes // steps
+    out = {"value": samples / (ms / 1e3), "unit": "samples/s", "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": eng.d2h_bytes // steps, "ms_per_step": ms / steps, "steps": steps,
+           "batch_rows_per_gpu": rows, "last_acc": results[-1][0] if results else None,
+           "h2d_gbs_per_gpu_achieved": h2d / (ms / steps / 1e3) / 1e9,
+           "api": "StreamingLogisticEngine.fit_stream (pinned host batches, double-buffered H2D, per-step D2H of accuracy+count)"}
+    # ceiling: the same pinned buffer, all ranks copying concurrently, nothing else running
+    dst = eng.bufs[0][0]
+    torch.cuda.synchronize()
+    dist.barrier()
+    a.record()
+    for _ in range(3):
+        dst[:rows].copy_(Xh, non_blocking=True)
+    b.record()
+    torch.cuda.synchronize()
+    cms = dist.max_over_ranks(a.elapsed_time(b)) / 3
+    out["h2d_gbs_per_gpu_ceiling"] = Xh.numel() * Xh.element_size() / (cms / 1e3) / 1e9
+    out["h2d_frac_of_ceiling"] = out["h2d_gbs_per_gpu_achieved"] / out["h2d_gbs_per_gpu_ceiling"]
+    return out
 
 
 def main():
@@ -206,27 +255,26 @@ def main():
     X, y, _ = synthetic_logistic_device(rows, args.dim, dev, dtype, seed=1000 + dist.rank)
     torch.cuda.synchronize()
     backend = "fused" if args.impl == "ours" else "nccl"
-    sampler = ClockSampler(gpu_index=dev.index or 0).start() if dist.is_main else None
-    if sampler:
-        sampler.stop()
-        sampler = ClockSampler(gpu_index=dev.index or 0)
-    head = bench_logistic(args, dist, "ssgd", args.steps, args.warmup, backend, X, y, sampler)
+    sampler = ClockSampler(gpu_index=dev.index or 0) if dist.is_main else None
+    head = bench_logistic(args, dist, "ssgd", args.steps, args.warmup, backend, X, y, sampler, keep_engine=True)
+    eng = head.pop("engine")
     clocks = sampler.summary() if sampler else {}
-    few = dist.max_over_ranks(1.0 if (dist.is_main and clocks.get("samples", 0) < 3) else 0.0) > 0
-    if few:
-        # the timed region is shorter than nvidia-smi's first sample: replay the SAME step for ~1.5 s (not timed,
-        # not reported; same step count on every rank) purely to record clocks / throttle reasons under that load
-        replay = max(50, int(1500.0 / max(head["ms_per_step"], 1e-3)))
-        if dist.is_main:
-            sampler = ClockSampler(gpu_index=dev.index or 0, period_ms=100).start()
-        for _ in range(replay):
-            head["engine"].step()
-        torch.cuda.synchronize()
-        dist.barrier()
-        if dist.is_main:
-            sampler.stop()
-            clocks = sampler.summary()
-            clocks["window"] = "%d-step replay of the timed step right after the timed region" % replay
+    checks = {}
+    # ---- sustained: replay the SAME step for >= 1 s, device-timed; clocks / throttle reasons are sampled over this window
+    #      as well when the K-step burst was shorter than nvidia-smi's first samples
+    replay = max(50, int(1000.0 / max(head["ms_per_step"], 1e-3))) if backend == "fused" else max(10, args.steps)
+    s2 = ClockSampler(gpu_index=dev.index or 0, period_ms=100) if dist.is_main else None
+    sus_ms = timed_steps(dist, eng.step, replay, 0, s2)
+    sustained = sus_ms / replay
+    if dist.is_main and clocks.get("samples", 0) < 3:
+        clocks = s2.summary()
+        clocks["window"] = "%d-step device-timed replay of the timed step right after the timed region" % replay
+    elif dist.is_main:
+        clocks["sustained_window"] = s2.summary()
+    # ---- check: after all those steps every rank must hold bit-identical weights (fixed-order in-kernel all-reduce)
+    crcs = dist.all_gather_object(crc_of(eng.w))
+    checks["w_bit_identical_across_ranks"] = bool(len(set(crcs)) == 1)
+    checks["w_finite"] = bool(torch.isfinite(eng.w).all().item())
     bytes_per_step = head["samples_per_s"] / dist.world * (head["ms_per_step"] / 1e3) * args.dim * X.element_size()
     out = {
         "metric": METRIC, "value": head["samples_per_s"], "unit": "samples/s", "n_gpus": dist.world,
@@ -239,14 +287,28 @@ def main():
                    "l2": "inputs >> L2: each step streams %.2f GB of sampled rows per GPU" % (bytes_per_step / 1e9),
                    "sampler": "Philox4x32-10 Bernoulli per row, fresh mask every step"},
         "clocks": clocks, "gpu_launches": head["launches"],
+        "sustained_ms_per_step": sustained, "sustained_steps": replay,
         "hbm_gbs_per_gpu": bytes_per_step / (head["ms_per_step"] / 1e3) / 1e9,
     }
+    if "finish_breakdown_last_step" in head:
+        out["finish_breakdown_last_step"] = head["finish_breakdown_last_step"]
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         out["roofline_frac_of_measured_hbm"] = out["hbm_gbs_per_gpu"] / peaks["hbm_gbs"]
     except Exception:
         pass
-    del head["engine"]
+    del eng
+    baseline = {}
+    want_base = args.impl == "ours" and not args.no_baseline
+    if want_base:
+        # ---- the in-box comparative arm: straightforward PyTorch + NCCL (+ cuBLAS) on the same rows and the same masks
+        try:
+            b = bench_logistic(args, dist, "ssgd", args.baseline_steps, 2, "nccl", X, y)
+            baseline["ssgd_samples_per_s"], baseline["ssgd_ms_per_step"] = b["samples_per_s"], b["ms_per_step"]
+            out["vs_baseline"] = head["samples_per_s"] / b["samples_per_s"]
+        except Exception as e:
+            baseline["ssgd_error"] = repr(e)[:200]
+        torch.cuda.empty_cache()
     extras = {}
     if not args.no_extras:
         for algo, st in (("easgd", max(3, args.steps // 2)), ("ma", max(2, args.steps // 5)), ("bmuf", max(2, args.steps // 5))):
@@ -254,7 +316,11 @@ def main():
                 r = bench_logistic(args, dist, algo, st, 2, backend, X, y)
                 extras[algo + "_samples_per_s"] = r["samples_per_s"]
                 extras[algo + "_ms_per_round"] = r["ms_per_step"]
-                del r["engine"]
+                if want_base:
+                    b = bench_logistic(args, dist, algo, 2, 1, "nccl", X, y)
+                    baseline[algo + "_samples_per_s"] = b["samples_per_s"]
+                    extras[algo + "_vs_baseline"] = r["samples_per_s"] / b["samples_per_s"]
+                    torch.cuda.empty_cache()
             except Exception as e:      # extras never take the headline down
                 extras[algo + "_error"] = repr(e)[:200]
     if not args.no_e2e and args.impl == "ours":
@@ -262,7 +328,6 @@ def main():
             out["e2e"] = bench_e2e(args, dist, X, y, args.e2e_steps, 2)
         except Exception as e:
             out["e2e"] = {"value": None, "error": repr(e)[:300]}
-    if not args.no_e2e and args.impl == "ours":
         try:    # additional view: the reference's dataflow (rows cached on the workers, w travels every step)
             out["e2e_resident"] = bench_e2e_resident(args, dist, X, y, max(args.steps, 10), 3)
         except Exception as e:
@@ -285,10 +350,13 @@ def main():
         torch.cuda.empty_cache()
         try:
             from benchmarks import extras as ex
-            extras.update(ex.run_all(dist, backend))
+            extras.update(ex.run_all(dist, backend, baseline=want_base, checks=checks,
+                                     pagerank={"scale": args.pagerank_scale}))
         except Exception as e:
             extras["extras_error"] = repr(e)[:300]
     out["extra"] = extras
+    out["baseline"] = baseline
+    out["checks"] = checks
     if dist.is_main:
         print(json.dumps(out))
         sys.stdout.flush()

@@ -307,7 +307,9 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       DAPB_RED4(0, 0, 1, 2, 3) DAPB_RED4(1, 4, 5, 6, 7) DAPB_RED4(2, 8, 9, 10, 11) DAPB_RED4(3, 12, 13, 14, 15)
       DAPB_RED4(4, 16, 17, 18, 19) DAPB_RED4(5, 20, 21, 22, 23) DAPB_RED4(6, 24, 25, 26, 27) DAPB_RED4(7, 28, 29, 30, 31)
 #undef DAPB_RED4
-      if (hm < m) { m = hm; m_group = group; }            // strict '<': the earlier (lower-index) group wins ties
+      // across groups only the DISTANCE part of the key is compared (key >> 5): on an exact tie the earlier group, i.e.
+      // the lower global centroid index, keeps the row -- the reference's strict '<' scan (k-means.py:25)
+      if ((hm >> 5) < (m >> 5)) { m = hm; m_group = group; }
       return m;
     };
 

@@ -7,7 +7,7 @@
 // Exactness: a 32-bit word u is read as the signed integer s = (int32)u, i.e. the coordinate
 // s / 2^31 in [-1, 1).  Acceptance x^2 + y^2 <= 1 is evaluated as sx^2 + sy^2 <= 2^62 in 64-bit
 // integer arithmetic, so the device count is bit-reproducible on the host.
-#include "common.cuh"
+#include "comm.cuh"
 #include "philox.cuh"
 
 using namespace dapb;
@@ -20,8 +20,20 @@ __device__ __forceinline__ unsigned accept_point(uint32_t ux, uint32_t uy) {
   return r2 <= (1ull << 62);
 }
 
+// Cross-GPU part (F7 "fused as last-block peer store", ref monte_carlo.py:28 reduce(add)): when `x.total_out` is set the
+// CTA that finishes last pushes this rank's count into slot [parity][rank] of every rank's heap (one multimem.st with
+// NVLS, else W peer stores), publishes the epoch flag, waits for the W flags and adds the W slots -- the job-wide total
+// is on every GPU when the kernel ends, no NCCL call.
+struct McXchg {
+  unsigned long long* total_out;   // null: single-GPU behaviour
+  uint32_t* ticket;                // 1 word, zero before first use
+  uint64_t payload_off;            // 2 * world u64 slots
+  uint32_t flag_base;              // `world` flags
+  uint64_t epoch;
+};
+
 __global__ void __launch_bounds__(256) mc_pi_kernel(uint64_t first, uint64_t n, uint64_t seed,
-                                                     unsigned long long* count_io) {
+                                                     unsigned long long* count_io, McXchg x, DapbComm c) {
   // counters [c0, c1): counter k covers samples 2k and 2k+1
   const uint64_t c_first = first >> 1, c_last = (first + n + 1) >> 1;   // exclusive
   const uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
@@ -44,6 +56,30 @@ __global__ void __launch_bounds__(256) mc_pi_kernel(uint64_t first, uint64_t n, 
     for (int w = 0; w < 8; ++w) t += s_part[w];
     if (t) atomicAdd(count_io, t);
   }
+  if (x.total_out == nullptr) return;
+  __shared__ bool s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned t = atomicAdd(x.ticket, 1u);
+    s_last = (t == gridDim.x - 1);
+    if (s_last) *x.ticket = 0;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const uint64_t par = (x.epoch & 1) * (uint64_t)c.world;
+  if (threadIdx.x == 0) {
+    const unsigned long long mine = atomicAdd(count_io, 0ull);
+    push_all<uint64_t>(c, x.payload_off, par + (uint64_t)c.rank, (uint64_t)mine);
+  }
+  block_barrier(c, c.rank, x.flag_base, x.epoch);
+  if (threadIdx.x == 0) {
+    const uint64_t* slots = reinterpret_cast<const uint64_t*>(comm_payload(c, c.rank, x.payload_off)) + par;
+    unsigned long long t = 0;
+    for (int r = 0; r < c.world; ++r) t += __ldcg(slots + r);
+    *x.total_out = t;
+  }
 }
 
 }  // namespace
@@ -55,7 +91,32 @@ extern "C" int dapb_mc_pi(uint64_t first, uint64_t n, uint64_t seed, unsigned lo
   uint64_t blocks = (counters + 255) / 256;
   const uint64_t cap = (uint64_t)dapb::sm_count() * 8;      // 8 resident CTAs of 256 threads per SM
   if (blocks > cap) blocks = cap;
-  mc_pi_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(first, n, seed, count_io);
+  McXchg x;
+  memset(&x, 0, sizeof(x));
+  DapbComm c;
+  memset(&c, 0, sizeof(c));
+  c.world = 1;
+  mc_pi_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(first, n, seed, count_io, x, c);
+  DAPB_LAUNCH_CHECK();
+  return 0;
+}
+
+// Same sampler, plus the job-wide total on every rank (see McXchg).  count_io: this rank's running count (zero it to
+// get this call's local count), total_out: device u64 that receives sum over ranks of count_io after this call.
+extern "C" int dapb_mc_pi_allreduce(const DapbComm* comm, uint64_t first, uint64_t n, uint64_t seed,
+                                    unsigned long long* count_io, unsigned long long* total_out, uint32_t* ticket,
+                                    uint64_t payload_off, uint32_t flag_base, uint64_t epoch, void* stream) {
+  DAPB_REQUIRE(comm && comm->world >= 1 && comm->world <= DAPB_MAX_RANKS, "mc_pi_allreduce: bad comm");
+  DAPB_REQUIRE(count_io && total_out && ticket && epoch >= 1, "mc_pi_allreduce: null argument / epoch starts at 1");
+  DAPB_REQUIRE(DAPB_FLAG_BYTES + payload_off + 2ull * comm->world * 8 <= comm->heap_bytes, "mc_pi_allreduce: heap too small");
+  const uint64_t counters = (n + 3) / 2;
+  uint64_t blocks = (counters + 255) / 256;
+  const uint64_t cap = (uint64_t)dapb::sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  McXchg x;
+  x.total_out = total_out; x.ticket = ticket; x.payload_off = payload_off; x.flag_base = flag_base; x.epoch = epoch;
+  mc_pi_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(first, n, seed, count_io, x, *comm);
   DAPB_LAUNCH_CHECK();
   return 0;
 }

@@ -251,7 +251,7 @@ __device__ __forceinline__ VT pr_warp_row_sum(const VT* __restrict__ c_cur, cons
 }
 
 template <typename VT>
-__global__ void __launch_bounds__(kPrThreads) pagerank_run_kernel(PrRunArgs<VT> a, DapbComm c) {
+__global__ void __launch_bounds__(kPrThreads, sizeof(VT) == 4 ? 6 : 4) pagerank_run_kernel(PrRunArgs<VT> a, DapbComm c) {
   __shared__ VT vals_all[kWarpsPerCta][kWarpCap];
   __shared__ bool s_last;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;

@@ -114,8 +114,10 @@ def _declare(lib: C.CDLL):
         "dapb_philox_mask": (C.c_int, [i64, i64, u64, u32, u32, vp, vp]),
         "dapb_lr_eval": (C.c_int, [vp, vp, i64, i32, i32, vp, f32, vp, vp, vp]),
         "dapb_mc_pi": (C.c_int, [u64, u64, u64, vp, vp]),
+        "dapb_mc_pi_allreduce": (C.c_int, [P(DapbComm), u64, u64, u64, vp, vp, vp, u64, u32, u64, vp]),
         "dapb_kmeans_assign": (C.c_int, [vp, i64, i32, i32, vp, i32, vp, vp, vp, vp]),
         "dapb_kmeans_finalize": (C.c_int, [P(DapbComm), vp, vp, vp, i32, i32, i32, u64, u32, u64, vp, i32, vp]),
+        "dapb_kmeans_finalize_tc": (C.c_int, [P(DapbComm), vp, vp, vp, i32, i32, u64, u32, u64, vp, i32, vp, vp, C.c_float, vp]),
         "dapb_kmeans_payload_bytes": (u64, [i32, i32, i32, i32]),
         "dapb_kmeans_tc_prepare": (C.c_int, [vp, i32, i32, vp, vp, C.c_float, vp]),
         "dapb_kmeans_assign_tc": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, vp, vp, i32, vp]),

@@ -101,6 +101,9 @@ class ShardedKMeans:
                 use_tc = kmeans_tc.supported(self.X, self.k)
             if use_tc:
                 self.tc = kmeans_tc.KMeansTC(self.X, self.k)
+            self._operand_ready = False         # tensor-core operands match self.centers (emitted by the finalize kernel)
+            # launches per Lloyd iteration in steady state: assignment + finalize (which emits the next operands)
+            self.launches_per_iter = 2
 
     def state_dict(self) -> dict:
         """Everything a resumed run needs (utils/checkpoint.py); replicated, so rank 0's copy is enough."""
@@ -109,6 +112,7 @@ class ShardedKMeans:
     def load_state_dict(self, st: dict):
         self.centers.copy_(torch.as_tensor(np.asarray(st["centers"]), dtype=self.acc_dtype))
         self.iteration = int(st["iteration"])
+        self._operand_ready = False
 
     def step(self):
         """One Lloyd iteration (ref k-means.py:55-71)."""
@@ -120,7 +124,14 @@ class ShardedKMeans:
         if self.backend == "fused":
             st = _native.stream_ptr()
             if self.tc is not None:
-                self.tc.assign_accumulate(self.centers, self.sums, self.counts)
+                self.tc.assign_accumulate(self.centers, self.sums, self.counts, prepared=self._operand_ready)
+                _native.check(self.lib.dapb_kmeans_finalize_tc(
+                    self.heap.comm_ref(), self.sums.data_ptr(), self.counts.data_ptr(), self.centers.data_ptr(), self.k,
+                    self.d, self.region.payload_off, self.region.flag_base, self.region.next_epoch(),
+                    self.counts_out.data_ptr(), 1, self.tc.b_operand.data_ptr(), self.tc.cnorm.data_ptr(),
+                    self.tc.xnorm_max, st), "kmeans_finalize_tc")
+                self._operand_ready = True
+                return
             else:
                 _native.check(self.lib.dapb_kmeans_assign(self.X.data_ptr(), self.n, self.d, _DT[self.X.dtype],
                                                           self.centers.data_ptr(), self.k, 0, self.sums.data_ptr(),
@@ -136,9 +147,21 @@ class ShardedKMeans:
             sums = torch.zeros(self.k, self.d, dtype=self.acc_dtype, device=self.X.device)
             cnt = torch.zeros(self.k, dtype=torch.int64, device=self.X.device)
             chunk = self._chunk_rows()
+            onehot_gemm = self.X.is_cuda and self.X.dtype in (torch.bfloat16, torch.float32) and self.k >= 64
             for i in range(0, self.n, chunk):
                 a = self._assign_torch(i, min(self.n, i + chunk))
-                sums.index_add_(0, a, self.X[i:i + chunk].to(self.acc_dtype))
+                x = self.X[i:i + chunk]
+                if onehot_gemm:
+                    # per-cluster sums as a second cuBLAS GEMM (one-hot^T @ X, fp32 accumulate and output): far faster
+                    # on a GPU than index_add_, whose atomics serialise on the k hot rows
+                    oh = torch.nn.functional.one_hot(a, self.k).to(x.dtype)
+                    try:
+                        sums += torch.mm(oh.T, x, out_dtype=torch.float32) if x.dtype != torch.float32 else oh.T @ x
+                    except (TypeError, RuntimeError):
+                        sums += (oh.T @ x).float()
+                    del oh
+                else:
+                    sums.index_add_(0, a, x.to(self.acc_dtype))
                 cnt += torch.bincount(a, minlength=self.k)
             cnt = cnt.to(self.acc_dtype)
             buf = torch.cat([sums, cnt[:, None]], dim=1)

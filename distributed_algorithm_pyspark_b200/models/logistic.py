@@ -451,6 +451,7 @@ class ShardedLogisticEngine:
         n_inner = 1 if cfg.algo == "easgd" else cfg.n_local_iterations
         for _ in range(n_inner):
             g, cnt = self._grad_nccl(self.w_local, keep)
+            self.last_count.fill_(cnt)
             if cnt > 0:
                 nw = self.w_local - cfg.eta * g / cnt
                 if cfg.algo == "easgd":

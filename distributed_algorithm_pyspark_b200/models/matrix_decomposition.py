@@ -184,7 +184,10 @@ class GramDecomposition:
     def gram(self) -> torch.Tensor:
         if self.backend == "fused":
             return self.tc() if self.tc is not None else self.op(self.A, self.A)
-        G = (self.A.T @ self.A).float()
+        try:        # cuBLAS bf16 GEMM with fp32 output (a bf16 output would round every entry of G to 8 bits)
+            G = torch.mm(self.A.T, self.A, out_dtype=torch.float32) if self.A.dtype != torch.float32 else self.A.T @ self.A
+        except (TypeError, RuntimeError):
+            G = (self.A.T @ self.A).float()
         self.dist.all_reduce_sum(G)
         return G
 

@@ -40,6 +40,26 @@ def accept_count_np(first: int, n: int, seed: int, chunk: int = 1 << 20) -> int:
     return total
 
 
+def mc_count_fused(first: int, n_local: int, seed: int, dist: Dist, heap=None, return_tensor: bool = False):
+    """Accepted samples over ALL ranks: sampler + grid reduction + cross-GPU total in one launch per rank
+    (csrc/monte_carlo.cu); the sum arrives through peer memory, ``torch.distributed`` is not involved."""
+    lib = _native.load()
+    dev = dist.device
+    cnt = torch.zeros(1, dtype=torch.int64, device=dev)
+    if dist.world == 1:
+        _native.check(lib.dapb_mc_pi(first, n_local, seed, cnt.data_ptr(), _native.stream_ptr()), "mc_pi")
+        return cnt if return_tensor else int(cnt.item())
+    from ..parallel.symm import default_heap
+    heap = heap or default_heap()
+    reg = heap.region("mc_pi_total", 2 * _native.MAX_RANKS * 8, _native.MAX_RANKS)
+    total = torch.zeros(1, dtype=torch.int64, device=dev)
+    ticket = torch.zeros(1, dtype=torch.int32, device=dev)
+    _native.check(lib.dapb_mc_pi_allreduce(heap.comm_ref(), first, n_local, seed, cnt.data_ptr(), total.data_ptr(),
+                                           ticket.data_ptr(), reg.payload_off, reg.flag_base, reg.next_epoch(),
+                                           _native.stream_ptr()), "mc_pi_allreduce")
+    return total if return_tensor else int(total.item())
+
+
 def run_monte_carlo(cfg: MonteCarloConfig, backend: str = "auto", dist: Optional[Dist] = None) -> Tuple[float, int]:
     """Returns (pi estimate, accepted count)."""
     if backend == "auto":
@@ -51,10 +71,8 @@ def run_monte_carlo(cfg: MonteCarloConfig, backend: str = "auto", dist: Optional
     a = (dist.rank * cfg.n) // dist.world
     b = ((dist.rank + 1) * cfg.n) // dist.world
     if backend == "fused":
-        lib = _native.load()
-        cnt = torch.zeros(1, dtype=torch.int64, device=dist.device)
-        _native.check(lib.dapb_mc_pi(a, b - a, seed, cnt.data_ptr(), _native.stream_ptr()), "mc_pi")
-        local = cnt
+        count = mc_count_fused(a, b - a, seed, dist)
+        return 4.0 * count / cfg.n, count
     else:   # torch baseline: torch.rand + all_reduce (different stream of random numbers, same estimator)
         g = torch.Generator(device=dist.device).manual_seed(seed + dist.rank)
         local = torch.zeros(1, dtype=torch.int64, device=dist.device)

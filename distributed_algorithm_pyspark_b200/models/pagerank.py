@@ -356,17 +356,39 @@ class ShardedPageRank:
                 _native.stream_ptr()), "pagerank_step")
             self._first = False
         else:
-            vals = self.c[g.col_idx.long()]
-            rows = torch.repeat_interleave(torch.arange(self.nv, device=vals.device), g.row_ptr[1:] - g.row_ptr[:-1])
-            s = torch.zeros(self.nv, dtype=self.dtype, device=vals.device)
-            s.index_add_(0, rows, vals)
-            if g.hub is not None and g.hub.rows.numel():          # long rows live outside the main CSR
-                h = g.hub
-                hrows = torch.repeat_interleave(h.rows.long(), h.ptr[1:] - h.ptr[:-1])
-                s.index_add_(0, hrows, self.c[h.col.long()])
+            s = self._spmv_baseline()
             r = torch.where(s > 0, base + damp * s, torch.zeros_like(s))
             self.ranks_local = r
             self.c = self._gather(r * self.inv)
+
+    def _spmv_baseline(self) -> torch.Tensor:
+        """s = A^T c for the owned rows.  On a GPU: cuSPARSE CSR SpMV through ``torch.sparse`` (the straightforward
+        library baseline; the matrices are built once); on CPU (gloo tests): gather + ``index_add_``."""
+        g = self.g
+        dev = g.row_ptr.device
+        if dev.type == "cuda":
+            if getattr(self, "_csr", None) is None:
+                ones = torch.ones(g.col_idx.numel(), dtype=self.dtype, device=dev)
+                self._csr = torch.sparse_csr_tensor(g.row_ptr, g.col_idx.long(), ones, size=(self.nv, g.V))
+                self._csr_hub = None
+                if g.hub is not None and g.hub.rows.numel():
+                    h = g.hub
+                    self._csr_hub = torch.sparse_csr_tensor(h.ptr, h.col.long(),
+                                                            torch.ones(h.col.numel(), dtype=self.dtype, device=dev),
+                                                            size=(h.rows.numel(), g.V))
+            s = torch.mv(self._csr, self.c)
+            if self._csr_hub is not None:
+                s.index_add_(0, g.hub.rows.long(), torch.mv(self._csr_hub, self.c))
+            return s
+        vals = self.c[g.col_idx.long()]
+        rows = torch.repeat_interleave(torch.arange(self.nv, device=vals.device), g.row_ptr[1:] - g.row_ptr[:-1])
+        s = torch.zeros(self.nv, dtype=self.dtype, device=vals.device)
+        s.index_add_(0, rows, vals)
+        if g.hub is not None and g.hub.rows.numel():          # long rows live outside the main CSR
+            h = g.hub
+            hrows = torch.repeat_interleave(h.rows.long(), h.ptr[1:] - h.ptr[:-1])
+            s.index_add_(0, hrows, self.c[h.col.long()])
+        return s
 
     def push_bytes_per_iter(self) -> int:
         """NVLink egress of this rank per iteration: vertices with in- AND out-edges x value size x copies."""

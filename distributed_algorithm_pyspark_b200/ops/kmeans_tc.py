@@ -35,10 +35,18 @@ class KMeansTC:
             xmax = max(xmax, float((xc * xc).sum(1).max().item()))
         self.xnorm_max = xmax
 
-    def assign_accumulate(self, centers: torch.Tensor, sums: torch.Tensor, counts: torch.Tensor, assign=None):
-        st = _native.stream_ptr()
+    def prepare(self, centers: torch.Tensor):
+        """fp32 centres -> bf16(-2c) operand + biased norms (only needed when the centres did not come out of
+        ``dapb_kmeans_finalize_tc``, which emits both itself)."""
         _native.check(self.lib.dapb_kmeans_tc_prepare(centers.data_ptr(), self.k, self.d, self.b_operand.data_ptr(),
-                                                      self.cnorm.data_ptr(), self.xnorm_max, st), "kmeans_tc_prepare")
+                                                      self.cnorm.data_ptr(), self.xnorm_max, _native.stream_ptr()),
+                      "kmeans_tc_prepare")
+
+    def assign_accumulate(self, centers: torch.Tensor, sums: torch.Tensor, counts: torch.Tensor, assign=None,
+                          prepared: bool = False):
+        st = _native.stream_ptr()
+        if not prepared:
+            self.prepare(centers)
         _native.check(self.lib.dapb_kmeans_assign_tc(self.X.data_ptr(), self.n, self.d, self.b_operand.data_ptr(),
                                                      self.cnorm.data_ptr(), self.k, _native.ptr(assign), sums.data_ptr(),
                                                      counts.data_ptr(), self.grid, st), "kmeans_assign_tc")

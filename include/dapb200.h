@@ -205,6 +205,12 @@ DAPB_API uint64_t dapb_lr_grad_noalloc_scratch_bytes(void);
  * Philox counter i/2; a point is accepted iff x^2+y^2 <= 1 evaluated exactly in integers.
  * count_io (device uint64) is atomically incremented. */
 DAPB_API int dapb_mc_pi(uint64_t first, uint64_t n, uint64_t seed, unsigned long long* count_io, void* stream);
+/* Same, fused with the cross-GPU total (ref :28 reduce(add)): the last CTA pushes this rank's count to every peer
+ * (multimem.st / peer stores), waits for the others and writes the sum over ranks to total_out (device u64).
+ * Needs 2*world u64 of payload, `world` flags, a zeroed ticket word; epoch +1 per call. */
+DAPB_API int dapb_mc_pi_allreduce(const DapbComm* comm, uint64_t first, uint64_t n, uint64_t seed,
+                                  unsigned long long* count_io, unsigned long long* total_out, uint32_t* ticket,
+                                  uint64_t payload_off, uint32_t flag_base, uint64_t epoch, void* stream);
 
 /* ------------------------------------------------------------------ F3 k-means ------------
  * ref: machine_learning/k-means.py:20-28,57-71.  dtype: 0 fp32, 1 bf16, 2 fp64 points; centres and
@@ -217,6 +223,12 @@ DAPB_API int dapb_kmeans_finalize(const DapbComm* comm, void* sums, int32_t* cou
                                   int32_t d, int32_t f64, uint64_t payload_off, uint32_t flag_base,
                                   uint64_t epoch, int32_t* counts_out, int32_t clear_partials, void* stream);
 DAPB_API uint64_t dapb_kmeans_payload_bytes(int32_t world, int32_t k, int32_t d, int32_t elem_bytes);
+/* Same for fp32 centres, and the finished centres are also emitted as the operands of dapb_kmeans_assign_tc (b_operand,
+ * cnorm: see dapb_kmeans_tc_prepare) -- a Lloyd iteration on the tensor-core path is then two launches: assign, finalize. */
+DAPB_API int dapb_kmeans_finalize_tc(const DapbComm* comm, void* sums, int32_t* counts, void* centers, int32_t k,
+                                     int32_t d, uint64_t payload_off, uint32_t flag_base, uint64_t epoch,
+                                     int32_t* counts_out, int32_t clear_partials, void* b_operand, float* cnorm,
+                                     float xnorm_max, void* stream);
 /* Tensor-core assignment (tcgen05.mma + TMEM + TMA), bf16 points, d in {64,128}, 1 <= k <= 16384; b_operand and cnorm
  * are sized for k_pad = k rounded up to a multiple of 128 ([k_pad, d] bf16 and k_pad + 8 floats).
  * dapb_kmeans_tc_prepare turns fp32 centres into the bf16 operand (-2c) [k,d] and the BIASED norms

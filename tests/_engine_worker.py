@@ -115,6 +115,19 @@ def main():
     torch.cuda.synchronize()
     out["kmeans_rel_diff"] = float((ka.centers - kb.centers).abs().max().item())
     out["kmeans_counts_equal"] = bool(torch.equal(ka.counts_out, kb.counts_out))
+    # counts beyond 2^24 per cluster must survive the cross-rank exchange exactly (they travel as integer bit patterns):
+    # feed the finalize kernel hand-made partial sums / counts
+    kk, dd = 24, 16
+    big = torch.full((kk,), 20_000_001 + dist.rank, dtype=torch.int32, device=dev)
+    psum = torch.ones(kk, dd, device=dev) * big[:, None].float()
+    cen = torch.zeros(kk, dd, device=dev)
+    cout = torch.zeros(kk, dtype=torch.int32, device=dev)
+    _native.check(lib.dapb_kmeans_finalize(heap.comm_ref(), psum.data_ptr(), big.data_ptr(), cen.data_ptr(), kk, dd, 0,
+                                           ka.region.payload_off, ka.region.flag_base, ka.region.next_epoch(),
+                                           cout.data_ptr(), 0, _native.stream_ptr()))
+    torch.cuda.synchronize()
+    want = sum(20_000_001 + r for r in range(dist.world))
+    out["kmeans_big_counts_exact"] = bool((cout == want).all().item())
     # ---- PageRank engine
     s, d = rmat_edges_np(12, 16, seed=3)
     src, dst = torch.as_tensor(s, device=dev), torch.as_tensor(d, device=dev)

@@ -1,5 +1,5 @@
 """Runs one tensor-core kernel check in its own process (a faulting kernel must not poison the pytest process).
-usage: _tc_worker.py kmeans n d k grid | gram n p grid | lr n D grid"""
+usage: _tc_worker.py kmeans n d k grid | kmeans_ties n d k | gram n p grid | lr n D grid"""
 import json
 import os
 import sys
@@ -41,6 +41,29 @@ def kmeans(n, d, k, grid):
     cnt_ok = bool(torch.equal(counts.long(), torch.bincount(got_c, minlength=k)))
     return {"n": n, "bad_range": bad_range, "wrong": wrong, "mismatch_vs_fp32": mism, "sum_rel_err": sum_err,
             "counts_ok": cnt_ok, "purity": float((got == lab).float().mean().item())}
+
+
+def kmeans_ties(n, d, k):
+    """Exact distance ties between centroids that sit in DIFFERENT 32-column groups of a chunk (and in different chunks):
+    duplicates of centroid j placed at j + 37 and j + 200 must never take a row -- lowest index wins (k-means.py:25)."""
+    from distributed_algorithm_pyspark_b200.ops.kmeans_tc import KMeansTC
+    dev = "cuda"
+    torch.manual_seed(7)
+    centres = (torch.randn(k, d, device=dev) * 3).to(torch.bfloat16).float()
+    dup_src = torch.arange(0, 20, device=dev)
+    centres[dup_src + 37] = centres[dup_src]
+    centres[dup_src + 200] = centres[dup_src]
+    lab = torch.randint(0, 20, (n,), device=dev)
+    X = (centres[lab] + 0.1 * torch.randn(n, d, device=dev)).to(torch.bfloat16).contiguous()
+    op = KMeansTC(X, k)
+    sums = torch.zeros(k, d, device=dev)
+    counts = torch.zeros(k, dtype=torch.int32, device=dev)
+    assign = torch.full((n,), -1, dtype=torch.int32, device=dev)
+    op.assign_accumulate(centres.contiguous(), sums, counts, assign)
+    torch.cuda.synchronize()
+    got = assign.long()
+    return {"to_duplicates": int(((got >= 37) & (got < 57)).sum().item() + ((got >= 200) & (got < 220)).sum().item()),
+            "to_originals": int((got < 20).sum().item()), "n": n}
 
 
 def gram(n, P, splits):
@@ -104,7 +127,7 @@ def lr(n, frac_pct, grid):
 def main():
     kind = sys.argv[1]
     args = list(map(int, sys.argv[2:]))
-    out = {"kmeans": kmeans, "gram": gram, "lr": lr}[kind](*args)
+    out = {"kmeans": kmeans, "kmeans_ties": kmeans_ties, "gram": gram, "lr": lr}[kind](*args)
     print("RESULT " + json.dumps(out))
 
 

@@ -38,6 +38,11 @@ def test_kmeans_tc_assignment_and_sums(n, d, k, grid):
     assert r["sum_rel_err"] < 1e-4 and r["counts_ok"], r
 
 
+def test_kmeans_tc_exact_ties_lowest_index_wins():
+    r = run_case("kmeans_ties", 20000, 128, 512)
+    assert r["to_duplicates"] == 0 and r["to_originals"] == r["n"], r
+
+
 @pytest.mark.parametrize("n,P,splits", [
     (64, 128, 1),              # one stage, one strip
     (64 * 7 + 13, 256, 2),     # ring wrap-around + ragged last tile, two strips

@@ -79,6 +79,7 @@ def test_engines_fused_vs_nccl_multi_gpu(tmp_path):
         assert r["bit_identical_across_ranks"], algo
     # fp32 near-ties may be assigned differently by the (x-c)^2 kernel and the ||c||^2 - 2x.c baseline
     assert out["kmeans_rel_diff"] < 1e-2
+    assert out["kmeans_big_counts_exact"]
     assert out["pagerank_rel_diff"] < 1e-3
     assert out["gram_rel_diff"] < 1e-4
     assert out["tc"] == [[337025, 18]] * 3, out["tc"]          # oracle: 337025 pairs after 18 rounds
