@@ -314,7 +314,7 @@ def run_all(dist, backend, only=None, baseline=False, checks=None, **kw):
             out.update(fn(dist, backend, baseline=baseline, checks=checks, **kw.get(name, {})))
         except Exception as e:                          # one failing extra must not hide the others
             out[name + "_error"] = repr(e)[:300]
-    if (not only or "pagerank" in only) and backend == "fused":
+    if (not only or "pagerank" in only) and backend == "fused" and not os.environ.get("DAPB_BENCH_SKIP_PR24"):
         try:    # continuity with round 1 (strong scaling of the smaller graph) + the N-GPU vs 1-GPU result check
             out.update(bench_pagerank(dist, backend, scale=24, iters=30, stats=False, tag="pagerank24"))
             if checks is not None:

@@ -172,101 +172,6 @@ __global__ void __launch_bounds__(256) sq_residual_kernel(const T* __restrict__ 
   if ((threadIdx.x & 31) == 0 && local != 0.0) atomicAdd(out, local);
 }
 
-// In-place lower Cholesky of a symmetric n x n fp32/fp64 matrix in global memory, blocked right-looking with
-// panels of kCb columns: per panel one single-CTA kernel factors the diagonal block in shared memory and solves
-// the rows below it, then a grid of 32 x 32 tiles applies the rank-kCb trailing update (only the lower triangle).
-// `info` = 1 + index of the first non-positive pivot, or 0.  The strict upper triangle is zeroed at the end.
-constexpr int kCb = 32;
-
-template <typename T>
-__global__ void __launch_bounds__(1024) chol_panel_kernel(T* __restrict__ A, int n, int j0, int* __restrict__ info) {
-  __shared__ T L[kCb][kCb + 1];
-  const int tid = threadIdx.x;
-  const int w = min(kCb, n - j0);
-  for (int i = tid; i < kCb * kCb; i += blockDim.x) {
-    const int r = i / kCb, cc = i % kCb;
-    L[r][cc] = (r < w && cc < w && cc <= r) ? A[(int64_t)(j0 + r) * n + j0 + cc] : (T)0;
-  }
-  __syncthreads();
-  for (int j = 0; j < w; ++j) {                         // unblocked factorisation of the w x w diagonal block
-    if (tid == 0) {
-      T d = L[j][j];
-      if (!(d > (T)0)) { if (*info == 0) *info = j0 + j + 1; d = (T)1; }
-      L[j][j] = sqrt(d);
-    }
-    __syncthreads();
-    if (tid > j && tid < w) L[tid][j] /= L[j][j];
-    __syncthreads();
-    for (int idx = tid; idx < w * w; idx += blockDim.x) {
-      const int r = idx / w, cc = idx % w;
-      if (cc > j && cc <= r) L[r][cc] -= L[r][j] * L[cc][j];
-    }
-    __syncthreads();
-  }
-  for (int i = tid; i < w * w; i += blockDim.x) {
-    const int r = i / w, cc = i % w;
-    if (cc <= r) A[(int64_t)(j0 + r) * n + j0 + cc] = L[r][cc];
-  }
-  // rows below the block: solve  X L11^T = A21  row by row (forward substitution), one thread per row
-  for (int r = j0 + w + tid; r < n; r += blockDim.x) {
-    T x[kCb];
-    for (int cc = 0; cc < w; ++cc) {
-      T s = A[(int64_t)r * n + j0 + cc];
-      for (int k = 0; k < cc; ++k) s -= x[k] * L[cc][k];
-      x[cc] = s / L[cc][cc];
-    }
-    for (int cc = 0; cc < w; ++cc) A[(int64_t)r * n + j0 + cc] = x[cc];
-  }
-}
-
-// A22[i, c] -= sum_k L21[i, k] L21[c, k] for the lower triangle of the trailing matrix (tiles of 32 x 32)
-template <typename T>
-__global__ void __launch_bounds__(256) chol_update_kernel(T* __restrict__ A, int n, int j0, int w) {
-  const int bi = blockIdx.y, bj = blockIdx.x;
-  if (bj > bi) return;
-  __shared__ T Li[32][kCb + 1], Lj[32][kCb + 1];
-  const int r0 = j0 + w + bi * 32, c0 = j0 + w + bj * 32;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;         // 32 x 8
-  for (int rr = ty; rr < 32; rr += 8) {
-    Li[rr][tx] = (r0 + rr < n && tx < w) ? A[(int64_t)(r0 + rr) * n + j0 + tx] : (T)0;
-    Lj[rr][tx] = (c0 + rr < n && tx < w) ? A[(int64_t)(c0 + rr) * n + j0 + tx] : (T)0;
-  }
-  __syncthreads();
-  for (int rr = ty; rr < 32; rr += 8) {
-    const int r = r0 + rr, cc = c0 + tx;
-    if (r < n && cc <= r) {
-      T s = 0;
-#pragma unroll
-      for (int k = 0; k < kCb; ++k) s += Li[rr][k] * Lj[tx][k];
-      A[(int64_t)r * n + cc] -= s;
-    }
-  }
-}
-
-template <typename T>
-__global__ void chol_zero_upper_kernel(T* __restrict__ A, int n) {
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < (int64_t)n * n; idx += (int64_t)gridDim.x * blockDim.x) {
-    const int i = (int)(idx / n), cc = (int)(idx % n);
-    if (cc > i) A[idx] = (T)0;
-  }
-}
-
-template <typename T>
-int cholesky_blocked(T* A, int n, int* info, cudaStream_t st) {
-  for (int j0 = 0; j0 < n; j0 += kCb) {
-    const int w = n - j0 < kCb ? n - j0 : kCb;
-    chol_panel_kernel<T><<<1, 1024, 0, st>>>(A, n, j0, info);
-    const int rem = n - j0 - w;
-    if (rem > 0) {
-      const int nb = (rem + 31) / 32;
-      chol_update_kernel<T><<<dim3(nb, nb), 256, 0, st>>>(A, n, j0, w);
-    }
-  }
-  chol_zero_upper_kernel<T><<<64, 256, 0, st>>>(A, n);
-  DAPB_LAUNCH_CHECK();
-  return 0;
-}
-
 template <typename T, typename TA>
 int launch_gram(const DapbComm* comm, const void* X, const void* Y, int64_t n, int P, int Q, int64_t ldx, int64_t ldy,
                 void* partial, int splits, void* C, uint32_t* ticket, uint64_t payload_off, uint32_t flag_base,
@@ -337,10 +242,4 @@ extern "C" int dapb_sq_residual(const void* R, const void* U, const void* V, int
   else sq_residual_kernel<float><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const float*)R, (const float*)U, (const float*)V, m, n, k, out);
   DAPB_LAUNCH_CHECK();
   return 0;
-}
-
-extern "C" int dapb_cholesky(void* A, int32_t n, int32_t f64, int32_t* info, void* stream) {
-  DAPB_REQUIRE(n >= 1 && n <= 4096 && info, "cholesky: bad arguments");
-  if (f64) return cholesky_blocked<double>((double*)A, n, info, (cudaStream_t)stream);
-  return cholesky_blocked<float>((float*)A, n, info, (cudaStream_t)stream);
 }

@@ -10,6 +10,7 @@
 // reference's toy data, tests and odd shapes.  The tcgen05 tensor-core assignment kernel for the
 // benchmark shape lives in kmeans_tc.cu and feeds the same finalize kernel.
 #include "comm.cuh"
+#include "kmeans_common.cuh"
 
 using namespace dapb;
 
@@ -78,7 +79,7 @@ __device__ __forceinline__ int dec_count(double v) { return (int)v; }
 // (assign, finalize) and no separate prepare pass exists.
 struct KmTcEmit {
   __nv_bfloat16* b_operand;   // [k_pad, d] or null
-  float* cnorm;               // [k_pad + 8]
+  float* cnorm;               // [9 * k_pad + 8], see kmeans_common.cuh
   int k_pad;
   float xnorm_max;
 };
@@ -114,8 +115,9 @@ __device__ void kmeans_emit_tc_operand(const TA* centers, int k, int d, const Km
   frexpf(M, &ex);
   const float C1 = ldexpf(1.5f, ex + 1);
   for (int j = tid; j < e.k_pad; j += blockDim.x) {
-    if (j < k) e.cnorm[j] += C1;
-    else e.cnorm[j] = C1 + ldexpf(0.9999f, ex);
+    const float v = j < k ? e.cnorm[j] + C1 : C1 + ldexpf(0.9999f, ex);
+    e.cnorm[j] = v;
+    kmeans_norm_slab_store(e.cnorm, e.k_pad, j, v);
   }
   if (tid == 0) { e.cnorm[e.k_pad] = cmax; e.cnorm[e.k_pad + 1] = C1; }
 }

@@ -4,8 +4,12 @@
 // ref math: machine_learning/k-means.py:20-28 (argmin_c ||x - c||, ties -> lowest index) and :57-63
 // (per-cluster vector sum and count).  argmin_c ||x - c||^2 == argmin_c (||c||^2 - 2 x.c); the cross term
 // for a 128-row tile against 128 centroids is one bf16 `tcgen05.mma` chain (M=128, N=128, K=d) whose fp32
-// accumulator lives in TMEM.  The centroid operand holds -2c, and the accumulator is PRE-LOADED (tcgen05.st) with
-// ||c_j||^2 + C1 in column j, so the tensor core itself delivers the biased distance C1 + ||c||^2 - 2 x.c.
+// accumulator lives in TMEM.  The centroid operand holds -2c, and the biased norm ||c_j||^2 + C1 enters the accumulator
+// through the tensor core as well: a ninth, K = 16 MMA multiplies a constant slab of ones (three 1s per row) with a
+// slab holding the norm split into three bf16 terms (hi + mid + lo = the fp32 value), and is issued FIRST with
+// accumulate = 0.  So the tensor core itself delivers the biased distance C1 + ||c||^2 - 2 x.c and the epilogue neither
+// loads norms nor writes TMEM (an earlier version pre-loaded the accumulators with tcgen05.st from broadcast LDS.128:
+// those loads alone took 47 % of the shared-memory pipe next to the tensor core's own operand reads).
 // C1 = 1.5 * 2^E is chosen (dapb_kmeans_tc_prepare, Cauchy-Schwarz bound from max ||x||^2 and max ||c||^2) so that
 // every biased distance lies in [2^E, 2^(E+1)): one common exponent, i.e. the bit patterns are fixed-point numbers
 // and key = bits * 32 + column-in-group orders like (distance, column) in unsigned arithmetic.  The epilogue is
@@ -43,6 +47,7 @@
 // Near-ties: distances are compared at a resolution of 2^(E-23) <= 4 M * 2^-23 (M = bound on |distance|), far below
 // the error already introduced by bf16 inputs; exact tie semantics need the CUDA-core path (kmeans.cu).
 #include "tc_common.cuh"
+#include "kmeans_common.cuh"
 
 using namespace dapb;
 using namespace dapb::tc;
@@ -53,23 +58,25 @@ constexpr int kTM = 128;          // rows per tile (UMMA M)
 constexpr int kNB = 128;          // centroids per chunk (UMMA N)
 constexpr int kSuper = 4;         // row tiles per super tile
 constexpr int kASlots = 4;
-constexpr int kBStages = 3;
+constexpr int kBSlots = 5;        // ring of centroid HALF-chunks (128 centroids x 64 features = 16 KB each)
+constexpr int kExtStages = 3;     // ring of norm slabs (128 centroids x K = 16, no swizzle, 4 KB each)
+constexpr uint32_t kExtBytes = kNB * 32;
 constexpr int kTBufs = 4;         // TMEM accumulator buffers (4 x 128 columns = 512)
 constexpr int kThreads = 512;        // 16 warps: 4 service warps, 2 x 4 arg-min warps, 4 scatter warps
 constexpr int kParts = kNB / 32;  // 32-column epilogue steps per accumulator
-constexpr int kCnStages = 2;      // ring of biased centroid-norm chunks in shared memory (source of the tcgen05.st pre-load)
 
 template <int KD>
 struct SmemLayout {
   static constexpr int kHalves = KD / 64;
   static constexpr uint32_t kATile = kTM * KD * 2;                 // bytes
-  static constexpr uint32_t kBChunk = kNB * KD * 2;
+  static constexpr uint32_t kBHalf = kNB * 128;                    // one half-chunk: 128 centroids x 64 features
   static constexpr uint32_t kAOff = 0;
   static constexpr uint32_t kBOff = kAOff + kASlots * kATile;
-  static constexpr uint32_t kCnOff = kBOff + kBStages * kBChunk;   // float[kCnStages][kNB] ring of ||c||^2 chunks
-  static constexpr uint32_t kAsOff = kCnOff + kCnStages * kNB * 4; // uint16[kASlots][128]
+  static constexpr uint32_t kExtOff = kBOff + kBSlots * kBHalf;    // [kExtStages][4 KB] norm slabs (K-major, no swizzle)
+  static constexpr uint32_t kOnesOff = kExtOff + kExtStages * kExtBytes;   // [128 rows x K = 16] ones slab, same layout
+  static constexpr uint32_t kAsOff = kOnesOff + kTM * 32;          // uint16[kASlots][128]
   static constexpr uint32_t kBarOff = kAsOff + kASlots * kTM * 2;
-  static constexpr int kNumBars = 4 * kASlots + 2 * kBStages + 2 * kTBufs + 2 * kCnStages;
+  static constexpr int kNumBars = 4 * kASlots + 2 * kBSlots + 2 * kTBufs + 2 * kExtStages;
   static constexpr uint32_t kTmemOff = kBarOff + kNumBars * 8;
   static constexpr uint32_t kTotal = kTmemOff + 16;
 };
@@ -78,7 +85,7 @@ struct KmTcArgs {
   const __nv_bfloat16* X; // [n, KD]
   int64_t n;              // rows
   int k;                  // centroids incl. padding (multiple of 128, <= 16384)
-  const float* cnorm;     // [k]
+  const float* cnorm;     // [k + 8 + 8 k]: biased norms, 8 aux words, then the K = 16 norm slabs (see kmeans_norm_slab)
   float* sums;            // [k, KD]
   int* counts;            // [k]
   int* assign;            // [n] or null
@@ -112,12 +119,11 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
   uint64_t* as_full = a_empty + kASlots;
   uint64_t* as_empty = as_full + kASlots;
   uint64_t* b_full = as_empty + kASlots;
-  uint64_t* b_empty = b_full + kBStages;
-  uint64_t* t_full = b_empty + kBStages;
+  uint64_t* b_empty = b_full + kBSlots;
+  uint64_t* t_full = b_empty + kBSlots;
   uint64_t* t_empty = t_full + kTBufs;
   uint64_t* cn_full = t_empty + kTBufs;
-  uint64_t* cn_empty = cn_full + kCnStages;
-  float* cn_s = reinterpret_cast<float*>(smem + L::kCnOff);
+  uint64_t* cn_empty = cn_full + kExtStages;
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(smem + L::kTmemOff);
   uint16_t* assign_s = reinterpret_cast<uint16_t*>(smem + L::kAsOff);
 
@@ -133,11 +139,20 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     for (int i = 0; i < kASlots; ++i) {
       mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); mbar_init(&as_full[i], 4); mbar_init(&as_empty[i], 4);
     }
-    for (int i = 0; i < kBStages; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 2); }   // two MMA issuers
+    for (int i = 0; i < kBSlots; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 2); }   // two MMA issuers
     for (int i = 0; i < kTBufs; ++i) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], 4); }
-    for (int i = 0; i < kCnStages; ++i) { mbar_init(&cn_full[i], 1); mbar_init(&cn_empty[i], 8); }
+    for (int i = 0; i < kExtStages; ++i) { mbar_init(&cn_full[i], 1); mbar_init(&cn_empty[i], 2); }
     fence_barrier_init();
   }
+  // ones slab: row r = (1, 1, 1, 0 x 13) bf16 in the canonical K-major no-swizzle form (8-row x 16-byte core matrices;
+  // the two K halves of a row group 128 B apart, row groups 256 B apart)
+  for (int i = threadIdx.x; i < kTM * 2; i += kThreads) {
+    const int r = i >> 1, kc = i & 1;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (kc == 0) { v.x = 0x3F803F80u; v.y = 0x00003F80u; }          // bf16 1.0 = 0x3F80
+    *reinterpret_cast<uint4*>(smem + L::kOnesOff + (r >> 3) * 256 + kc * 128 + (r & 7) * 16) = v;
+  }
+  fence_proxy_async();
   if (warp == 2) { tmem_alloc(tmem_holder, 512); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
@@ -168,29 +183,30 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     // ===================== TMA producer: centroid chunks (warp 0, lane 1) =====================
     {
       prefetch_tensormap(&map_c);
-      uint32_t j = 0;
+      uint32_t j = 0;                                    // half-chunks loaded so far
       for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
-        for (int c = 0; c < n_chunks; ++c, ++j) {
-          const uint32_t st = j % kBStages, use = j / kBStages;
-          DAPB_T(pc0, mbar_wait(&b_empty[st], (use & 1) ^ 1));
-          mbar_arrive_expect_tx(&b_full[st], L::kBChunk);
-          uint8_t* dst = smem + L::kBOff + st * L::kBChunk;
+        for (int c = 0; c < n_chunks; ++c) {
 #pragma unroll
-          for (int h = 0; h < L::kHalves; ++h)
-            tma_load_2d_hint(dst + h * (kNB * 128), &map_c, &b_full[st], h * 64, c * kNB, kEvictLast);
+          for (int h = 0; h < L::kHalves; ++h, ++j) {
+            const uint32_t st = j % kBSlots, use = j / kBSlots;
+            DAPB_T(pc0, mbar_wait(&b_empty[st], (use & 1) ^ 1));
+            mbar_arrive_expect_tx(&b_full[st], L::kBHalf);
+            tma_load_2d_hint(smem + L::kBOff + st * L::kBHalf, &map_c, &b_full[st], h * 64, c * kNB, kEvictLast);
+          }
         }
       }
     }
   } else if (warp == 0 && lane == 2) {
-    // ===================== producer: ||c||^2 chunks for the arg-min warps (warp 0, lane 2) =====================
+    // ===================== producer: K = 16 norm slabs for the MMA issuers (warp 0, lane 2) =====================
     {
+      const char* ext = reinterpret_cast<const char*>(a.cnorm + a.k + 8);
       uint32_t j = 0;
       for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
         for (int c = 0; c < n_chunks; ++c, ++j) {
-          const uint32_t st = j % kCnStages, use = j / kCnStages;
+          const uint32_t st = j % kExtStages, use = j / kExtStages;
           mbar_wait(&cn_empty[st], (use & 1) ^ 1);
-          mbar_arrive_expect_tx(&cn_full[st], kNB * 4);
-          bulk_copy_g2s(cn_s + st * kNB, a.cnorm + c * kNB, kNB * 4, &cn_full[st]);
+          mbar_arrive_expect_tx(&cn_full[st], kExtBytes);
+          bulk_copy_g2s(smem + L::kExtOff + st * kExtBytes, ext + (size_t)c * kExtBytes, kExtBytes, &cn_full[st]);
         }
       }
     }
@@ -202,6 +218,10 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       constexpr uint32_t idesc = make_idesc_bf16(kTM, kNB, 0, 0);
       const uint64_t desc_tmpl = make_smem_desc_sw128(0, 16, 1024);
       const uint32_t a_base = smem_u32(smem + L::kAOff), b_base = smem_u32(smem + L::kBOff);
+      // K-major, no swizzle: LBO (K-adjacent core matrices) = 128 B, SBO (row groups) = 256 B
+      const uint64_t nosw_tmpl = ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | ((uint64_t)1 << 46);
+      const uint64_t d_ones = nosw_tmpl | (uint64_t)((smem_u32(smem + L::kOnesOff) & 0x3FFFF) >> 4);
+      const uint32_t ext_base = smem_u32(smem + L::kExtOff);
       const int mma_id = warp == 1 ? 0 : 1;
       uint32_t g0 = 0, j = 0, q0 = 0;                    // tiles / chunks / accumulators before this super tile
       // only lane 0 runs the loop: 32 lanes polling the mbarriers measurably slows the whole SM down (18.1 vs 8.9 ms)
@@ -210,34 +230,47 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         const int64_t tile0 = s * kSuper;
         constexpr int nt = kSuper;            // the last super tile is processed in full, rows beyond n are masked
         for (int c = 0; c < n_chunks; ++c, ++j) {
-          const uint32_t st = j % kBStages;
-          DAPB_T(pc0, mbar_wait(&b_full[st], (j / kBStages) & 1));
+          const uint32_t est = j % kExtStages;
+          uint32_t bst[L::kHalves];
+          DAPB_T(pc0, {
+            mbar_wait(&cn_full[est], (j / kExtStages) & 1);
+#pragma unroll
+            for (int h = 0; h < L::kHalves; ++h) {
+              const uint32_t jh = j * L::kHalves + h;
+              bst[h] = jh % kBSlots;
+              mbar_wait(&b_full[bst[h]], (jh / kBSlots) & 1);
+            }
+          });
+          const uint64_t d_ext = nosw_tmpl | (uint64_t)(((ext_base + est * kExtBytes) & 0x3FFFF) >> 4);
           for (int t = mma_id; t < nt; t += 2) {
             const uint32_t g = g0 + t, slot = g % kASlots;
             const uint32_t q = q0 + (uint32_t)(c * nt + t);
             if (c == 0) DAPB_T(pc1, mbar_wait(&a_full[slot], (g / kASlots) & 1));
             const uint32_t buf = q % kTBufs;
-            DAPB_T(pc2, mbar_wait(&t_empty[buf], (q / kTBufs) & 1));   // pre-loaded with the biased norms
+            DAPB_T(pc2, mbar_wait(&t_empty[buf], ((q / kTBufs) & 1) ^ 1));   // drained by the arg-min warps (first use passes)
             tc_fence_after();
-            // descriptors differ only in the 14-bit start-address field: build the two bases once per step and
-            // add compile-time offsets (units of 16 bytes) for the K halves / K steps
+            // descriptors differ only in the 14-bit start-address field: build the bases once per step and
+            // add compile-time offsets (units of 16 bytes) for the K steps
             const uint64_t da0 = desc_tmpl | (uint64_t)(((a_base + slot * L::kATile) & 0x3FFFF) >> 4);
-            const uint64_t db0 = desc_tmpl | (uint64_t)(((b_base + st * L::kBChunk) & 0x3FFFF) >> 4);
             const uint32_t d_tmem = tmem_base + buf * kNB;
             DAPB_T(pc3, {
+              umma_bf16(d_tmem, d_ones, d_ext, idesc, 0u);           // accumulator := ||c||^2 + C1 in every row
 #pragma unroll
-              for (int h = 0; h < L::kHalves; ++h)
+              for (int h = 0; h < L::kHalves; ++h) {
+                const uint64_t db0 = desc_tmpl | (uint64_t)(((b_base + bst[h] * L::kBHalf) & 0x3FFFF) >> 4);
 #pragma unroll
                 for (int ks = 0; ks < 4; ++ks)
-                  umma_bf16(d_tmem, da0 + (uint64_t)((h * (kTM * 128) + ks * 32) >> 4),
-                            db0 + (uint64_t)((h * (kNB * 128) + ks * 32) >> 4), idesc, 1u);
+                  umma_bf16(d_tmem, da0 + (uint64_t)((h * (kTM * 128) + ks * 32) >> 4), db0 + (uint64_t)((ks * 32) >> 4), idesc, 1u);
+              }
             });
             DAPB_T(pc4, {
               umma_commit(&t_full[buf]);
               if (c == n_chunks - 1) umma_commit(&a_empty[slot]);   // tensor core is done reading this X tile
             });
           }
-          umma_commit(&b_empty[st]);                               // this issuer is done with the centroid chunk
+#pragma unroll
+          for (int h = 0; h < L::kHalves; ++h) umma_commit(&b_empty[bst[h]]);   // this issuer is done with the centroid chunk
+          umma_commit(&cn_empty[est]);
         }
         g0 += nt;
         q0 += (uint32_t)(n_chunks * nt);
@@ -255,7 +288,7 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     const int row = qd * 32 + lane;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(qd * 32) << 16);
     const uint32_t kmul = a.key_mul;
-    uint32_t g0 = 0, q0 = 0, ji = 0;                      // tiles / accumulators before this super tile; norm chunks used
+    uint32_t g0 = 0, q0 = 0;                              // tiles / accumulators before this super tile
     uint32_t vA[32], vB[32];
 
     auto issue_load = [&](uint32_t qq, int part, uint32_t* v) {
@@ -266,25 +299,9 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       }
       tmem_ld_32x32b_x32(lane_addr + buf * kNB + part * 32, v);
     };
-    // Accumulators are PRE-LOADED with the biased norms ||c_j||^2 + C1 of the chunk they will receive next (all rows of
-    // a column hold the same value) and every MMA accumulates, so what comes back from TMEM already is
-    // C1 + ||c||^2 - 2 x.c: no norm add, no shared-memory operand in the reduction.  The 32 columns a tcgen05.ld has
-    // just drained are re-initialised at once by the same warp (its own 32 TMEM lanes).
-    auto init_part = [&](uint32_t buf, int part, const float* cnx) {
-      const uint4* c4 = reinterpret_cast<const uint4*>(cnx + part * 32);
-#pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-        uint32_t w[16];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const uint4 t = c4[hh * 4 + i];
-          w[4 * i] = t.x; w[4 * i + 1] = t.y; w[4 * i + 2] = t.z; w[4 * i + 3] = t.w;
-        }
-        tmem_st_32x32b_x16(lane_addr + buf * kNB + part * 32 + hh * 16, w);
-      }
-    };
-    auto release_buf = [&](uint32_t buf) {                // initialised (or simply drained): hand it to the MMA issuer
-      tmem_st_wait();
+    // What comes back from TMEM already is C1 + ||c||^2 - 2 x.c (the norm MMA opened the accumulation), so the epilogue
+    // is pure register work: no norm add, no shared-memory operand, no TMEM write.
+    auto release_buf = [&](uint32_t buf) {                // drained into registers: hand it back to the MMA issuers
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&t_empty[buf]);
@@ -314,51 +331,29 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     };
 
     // number of super tiles of this CTA (all are processed as FULL super tiles: rows beyond n are masked on output)
-    const int64_t my_super = n_super > blockIdx.x ? (n_super - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-    if (my_super > 0) {                                   // prologue: first two accumulators of this group <- chunk 0
-      mbar_wait(&cn_full[0], 0);
-      for (int tt = 0; tt < 2; ++tt) {
-        for (int part = 0; part < kParts; ++part) init_part(t_lo + tt, part, cn_s);
-        release_buf(t_lo + tt);
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&cn_empty[0]);
-      ji = 1;
-    }
-    int64_t s_idx = 0;
-    for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x, ++s_idx) {
+    for (int64_t s = blockIdx.x; s < n_super; s += gridDim.x) {
       const int64_t tile0 = s * kSuper;
       uint32_t best0 = 0xffffffffu, best1 = 0xffffffffu;
       int bgrp0 = 0, bgrp1 = 0;
       // accumulator index of (chunk c, row tile t) in this super tile: q0 + c * kSuper + t, TMEM buffer = t
       issue_load(q0 + t_lo, 0, vA);
       for (int c = 0; c < n_chunks; ++c) {
-        // the accumulator that follows (c, t) in buffer t is (c + 1, t), or (0, t) of the next super tile
-        const bool has_init = c + 1 < n_chunks || s_idx + 1 < my_super;
-        const uint32_t cst = ji % kCnStages;
-        if (has_init) mbar_wait(&cn_full[cst], (ji / kCnStages) & 1);
-        const float* cnx = cn_s + cst * kNB;
         auto drain = [&](const int tt, uint32_t& bst, int& bg) {
           const uint32_t qq = q0 + c * kSuper + t_lo + tt, buf = qq % kTBufs;
           const uint32_t qn = tt == 0 ? qq + 1 : qq + kSuper - 1;
           const bool has_next = tt == 0 || c + 1 < n_chunks;
-          DAPB_T(pc1, tmem_ld_wait()); if (has_init) init_part(buf, 0, cnx); issue_load(qq, 1, vB);
+          DAPB_T(pc1, tmem_ld_wait()); issue_load(qq, 1, vB);
           bst = reduce(vA, c * kParts + 0, bst, bg);
-          DAPB_T(pc1, tmem_ld_wait()); if (has_init) init_part(buf, 1, cnx); issue_load(qq, 2, vA);
+          DAPB_T(pc1, tmem_ld_wait()); issue_load(qq, 2, vA);
           bst = reduce(vB, c * kParts + 1, bst, bg);
-          DAPB_T(pc1, tmem_ld_wait()); if (has_init) init_part(buf, 2, cnx); issue_load(qq, 3, vB);
+          DAPB_T(pc1, tmem_ld_wait()); issue_load(qq, 3, vB);
           bst = reduce(vA, c * kParts + 2, bst, bg);
-          DAPB_T(pc1, tmem_ld_wait()); if (has_init) { init_part(buf, 3, cnx); release_buf(buf); }
+          DAPB_T(pc1, tmem_ld_wait()); release_buf(buf);       // all 128 columns of this accumulator are in registers
           if (has_next) issue_load(qn, 0, vA);
           bst = reduce(vB, c * kParts + 3, bst, bg);
         };
         drain(0, best0, bgrp0);
         drain(1, best1, bgrp1);
-        if (has_init) {
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&cn_empty[cst]);     // this warp is done with that chunk's norms
-          ++ji;
-        }
       }
 #pragma unroll
       for (int tt = 0; tt < 2; ++tt) {
@@ -474,8 +469,11 @@ __global__ void kmeans_tc_bias_kernel(float* __restrict__ cnorm, int k, int k_pa
   frexpf(M, &e);                                  // M = f * 2^e, f in [0.5, 1)  =>  M < 2^e
   const float C1 = ldexpf(1.5f, e + 1);           // E = e + 1: 2^(E-1) = 2^e > M
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j < k) cnorm[j] += C1;
-  else if (j < k_pad) cnorm[j] = C1 + ldexpf(0.9999f, e);
+  if (j < k_pad) {
+    const float v = j < k ? cnorm[j] + C1 : C1 + ldexpf(0.9999f, e);
+    cnorm[j] = v;
+    kmeans_norm_slab_store(cnorm, k_pad, j, v);       // what the assignment kernel's norm MMA reads
+  }
   if (j == 0) cnorm[k_pad + 1] = C1;
 }
 
@@ -492,8 +490,8 @@ int launch_km(const CUtensorMap& mx, const CUtensorMap& mc, KmTcArgs a, int grid
 
 }  // namespace
 
-// k_pad = k rounded up to a multiple of 128 (the MMA's N); b_operand: [k_pad, d] bf16; cnorm: [k_pad + 8] floats
-// (k_pad biased norms, then the running max and the bias, see above); xnorm_max >= max_i ||x_i||^2 over every row the
+// k_pad = k rounded up to a multiple of 128 (the MMA's N); b_operand: [k_pad, d] bf16; cnorm: 9 * k_pad + 8 floats
+// (k_pad biased norms, the running max and the bias, then the K = 16 norm slabs, see kmeans_common.cuh); xnorm_max >= max_i ||x_i||^2 over every row the
 // assignment kernel will see (a looser bound only costs resolution).
 extern "C" int dapb_kmeans_tc_prepare(const float* centers, int32_t k, int32_t d, void* b_operand, float* cnorm,
                                       float xnorm_max, void* stream) {

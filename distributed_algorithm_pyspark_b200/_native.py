@@ -138,6 +138,8 @@ def _declare(lib: C.CDLL):
         "dapb_solve_rows": (C.c_int, [vp, f64, vp, i64, i32, i32, vp, vp]),
         "dapb_sq_residual": (C.c_int, [vp, vp, vp, i64, i32, i32, i32, vp, vp]),
         "dapb_cholesky": (C.c_int, [vp, i32, i32, vp, vp]),
+        "dapb_cholesky_dbg": (C.c_int, [vp, i32, i32, vp, vp, vp]),
+        "dapb_eigh": (C.c_int, [vp, i32, i32, vp, vp, vp, C.c_float, i32, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name, None)

@@ -361,13 +361,27 @@ class ShardedPageRank:
             self.ranks_local = r
             self.c = self._gather(r * self.inv)
 
-    def _spmv_baseline(self) -> torch.Tensor:
-        """s = A^T c for the owned rows.  On a GPU: cuSPARSE CSR SpMV through ``torch.sparse`` (the straightforward
-        library baseline; the matrices are built once); on CPU (gloo tests): gather + ``index_add_``."""
+    def _spmv_gather(self) -> torch.Tensor:
+        g = self.g
+        vals = self.c[g.col_idx.long()]
+        if getattr(self, "_rows_idx", None) is None:
+            self._rows_idx = torch.repeat_interleave(torch.arange(self.nv, device=vals.device), g.row_ptr[1:] - g.row_ptr[:-1])
+            self._hub_rows_idx = None
+            if g.hub is not None and g.hub.rows.numel():
+                self._hub_rows_idx = torch.repeat_interleave(g.hub.rows.long(), g.hub.ptr[1:] - g.hub.ptr[:-1])
+        s = torch.zeros(self.nv, dtype=self.dtype, device=vals.device)
+        s.index_add_(0, self._rows_idx, vals)
+        if self._hub_rows_idx is not None:                    # long rows live outside the main CSR
+            s.index_add_(0, self._hub_rows_idx, self.c[g.hub.col.long()])
+        return s
+
+    def _spmv_csr(self) -> torch.Tensor:
         g = self.g
         dev = g.row_ptr.device
-        if dev.type == "cuda":
-            if getattr(self, "_csr", None) is None:
+        if getattr(self, "_csr", None) is None:
+            import warnings
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
                 ones = torch.ones(g.col_idx.numel(), dtype=self.dtype, device=dev)
                 self._csr = torch.sparse_csr_tensor(g.row_ptr, g.col_idx.long(), ones, size=(self.nv, g.V))
                 self._csr_hub = None
@@ -376,19 +390,39 @@ class ShardedPageRank:
                     self._csr_hub = torch.sparse_csr_tensor(h.ptr, h.col.long(),
                                                             torch.ones(h.col.numel(), dtype=self.dtype, device=dev),
                                                             size=(h.rows.numel(), g.V))
-            s = torch.mv(self._csr, self.c)
-            if self._csr_hub is not None:
-                s.index_add_(0, g.hub.rows.long(), torch.mv(self._csr_hub, self.c))
-            return s
-        vals = self.c[g.col_idx.long()]
-        rows = torch.repeat_interleave(torch.arange(self.nv, device=vals.device), g.row_ptr[1:] - g.row_ptr[:-1])
-        s = torch.zeros(self.nv, dtype=self.dtype, device=vals.device)
-        s.index_add_(0, rows, vals)
-        if g.hub is not None and g.hub.rows.numel():          # long rows live outside the main CSR
-            h = g.hub
-            hrows = torch.repeat_interleave(h.rows.long(), h.ptr[1:] - h.ptr[:-1])
-            s.index_add_(0, hrows, self.c[h.col.long()])
+        s = torch.mv(self._csr, self.c)
+        if self._csr_hub is not None:
+            s.index_add_(0, g.hub.rows.long(), torch.mv(self._csr_hub, self.c))
         return s
+
+    def _spmv_baseline(self) -> torch.Tensor:
+        """s = A^T c for the owned rows, baseline arm.  Two straightforward library formulations exist -- cuSPARSE CSR
+        SpMV through ``torch.sparse`` and gather + ``index_add_`` -- and which one wins depends on graph and torch
+        build, so on a GPU both are timed once (second call of each) and the faster one is kept: the baseline is
+        the better of the two.  CPU (gloo tests): gather + ``index_add_``."""
+        if self.g.row_ptr.device.type != "cuda" or self.g.col_idx.numel() < (1 << 16):
+            return self._spmv_gather()
+        if getattr(self, "_spmv_choice", None) is None:
+            times = {}
+            for name, fn in (("gather", self._spmv_gather), ("csr", self._spmv_csr)):
+                try:
+                    fn()
+                    torch.cuda.synchronize()
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                    fn()
+                    b.record()
+                    torch.cuda.synchronize()
+                    times[name] = a.elapsed_time(b)
+                except Exception:          # noqa: BLE001 -- e.g. sparse CSR unsupported for this dtype
+                    pass
+            # every rank must take the same code path length-wise? no collective inside: a per-rank choice is fine
+            self._spmv_choice = min(times, key=times.get) if times else "gather"
+            if self._spmv_choice == "gather":
+                self._csr = self._csr_hub = None
+            else:
+                self._rows_idx = self._hub_rows_idx = None
+        return self._spmv_csr() if self._spmv_choice == "csr" else self._spmv_gather()
 
     def push_bytes_per_iter(self) -> int:
         """NVLink egress of this rank per iteration: vertices with in- AND out-edges x value size x copies."""

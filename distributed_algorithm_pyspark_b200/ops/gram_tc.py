@@ -6,10 +6,12 @@ import torch
 from .. import _native
 
 
-def supported(A: torch.Tensor) -> bool:
+def supported(A: torch.Tensor, world: int = 1) -> bool:
     lib = _native.load()
     if not hasattr(lib, "dapb_gram_tc"):
         return False
+    if A.dim() == 2 and (A.shape[1] * A.shape[1]) % (4 * max(world, 1)):
+        return False                    # the in-kernel two-shot all-reduce cuts G into `world` slices of float4s
     return (A.is_cuda and A.dtype == torch.bfloat16 and A.dim() == 2 and A.is_contiguous() and A.shape[1] in (128, 256, 512)
             and A.shape[0] >= 64 and A.data_ptr() % 16 == 0)
 
@@ -25,7 +27,7 @@ class GramTC:
         self.n, self.P = A.shape
         self.splits = splits
         self.G = torch.zeros(self.P, self.P, dtype=torch.float32, device=A.device)
-        self.tickets = torch.zeros(self.P // 128, dtype=torch.int32, device=A.device)
+        self.tickets = torch.zeros(1024, dtype=torch.int32, device=A.device)      # DAPB_GRAM_TC_SCRATCH_WORDS
         self.region = None
         from ..parallel.symm import default_heap
         self.heap = heap or default_heap()

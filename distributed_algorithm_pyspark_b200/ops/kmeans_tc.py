@@ -25,7 +25,7 @@ class KMeansTC:
         self.grid = grid
         k_pad = (self.k + 127) // 128 * 128                     # the MMA's N granularity; padding centroids never win
         self.b_operand = torch.empty(k_pad, self.d, dtype=torch.bfloat16, device=X.device)
-        self.cnorm = torch.empty(k_pad + 8, dtype=torch.float32, device=X.device)
+        self.cnorm = torch.empty(9 * k_pad + 8, dtype=torch.float32, device=X.device)      # norms + aux + K=16 norm slabs
         # max ||x||^2 over the resident shard (X never changes): bounds every distance, so the kernel can compare
         # fixed-exponent bit patterns instead of floats.  One chunked pass at construction.
         xmax = 0.0

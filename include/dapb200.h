@@ -230,7 +230,8 @@ DAPB_API int dapb_kmeans_finalize_tc(const DapbComm* comm, void* sums, int32_t* 
                                      int32_t* counts_out, int32_t clear_partials, void* b_operand, float* cnorm,
                                      float xnorm_max, void* stream);
 /* Tensor-core assignment (tcgen05.mma + TMEM + TMA), bf16 points, d in {64,128}, 1 <= k <= 16384; b_operand and cnorm
- * are sized for k_pad = k rounded up to a multiple of 128 ([k_pad, d] bf16 and k_pad + 8 floats).
+ * are sized for k_pad = k rounded up to a multiple of 128 ([k_pad, d] bf16 and 9 * k_pad + 8 floats: the biased norms,
+ * 8 aux words and the K = 16 bf16 norm slabs that feed the norm to the tensor core, csrc/kmeans_common.cuh).
  * dapb_kmeans_tc_prepare turns fp32 centres into the bf16 operand (-2c) [k,d] and the BIASED norms
  * ||bf16(c)||^2 + C1 in cnorm[0..k) (C1 makes all distances share one exponent so that the
  * arg-min runs on integer keys, see csrc/kmeans_tc.cu).  xnorm_max: an upper bound on ||x||^2 over all rows. */
@@ -333,7 +334,11 @@ DAPB_API int dapb_gram(const DapbComm* comm, const void* X, const void* Y, int64
                        uint32_t* ticket, uint64_t payload_off, uint32_t flag_base, uint64_t epoch,
                        int32_t do_allreduce, void* stream);
 /* Tensor-core Gram (tcgen05.mma, MN-major operands straight from one TMA tile): G = A^T A, A [n_rows, P] bf16,
- * P in {128, 256, 512}; row splits are reduced with vector atomics, ranks with an in-kernel one-shot all-reduce. */
+ * P in {128, 256, 512}.  Only the blocks on and above the diagonal are computed (SYRK schedule) and mirrored by the
+ * epilogue; row splits are reduced with atomics, ranks with a grid-wide in-kernel two-shot all-reduce (multimem when the
+ * heap is multicast-mapped) that needs dapb_gram_tc_payload_bytes of heap, `world` flags and P*P % (4*world) == 0.
+ * `tickets`: DAPB_GRAM_TC_SCRATCH_WORDS words of scratch.  epoch +1 per call. */
+#define DAPB_GRAM_TC_SCRATCH_WORDS 1024
 DAPB_API int dapb_gram_tc(const DapbComm* comm, const void* A, int64_t n_rows, int32_t P, float* G, uint32_t* tickets,
                           int32_t splits, uint64_t payload_off, uint32_t flag_base, uint64_t epoch,
                           int32_t do_allreduce, void* stream);
@@ -344,7 +349,15 @@ DAPB_API int dapb_solve_rows(const void* G, double ridge, const void* B, int64_t
                              void* X, void* stream);
 DAPB_API int dapb_sq_residual(const void* R, const void* U, const void* V, int64_t m, int32_t n, int32_t k,
                               int32_t f64, double* out, void* stream);
+/* In-place lower Cholesky (strict upper triangle zeroed), ONE cooperative launch (csrc/dense_small.cu); info (device int,
+ * zero it first) = 1 + index of the first non-positive pivot, or 0. */
 DAPB_API int dapb_cholesky(void* A, int32_t n, int32_t f64, int32_t* info, void* stream);
+/* Symmetric eigen-decomposition by block one-sided Jacobi, one cooperative launch after a small init kernel; no cuSOLVER.
+ * G [n, n] fp32 / fp64 (its symmetric part is used), n % 8 == 0 and n <= 800 (fp32) / 400 (fp64) for the widest block.
+ * work: 2*n*n elements + 16 bytes; evals [n] ascending; evecs [n, n] row-major, eigenvector j in column j.
+ * tol <= 0 and max_sweeps <= 0 select defaults; sweeps_out (device int32) is optional. */
+DAPB_API int dapb_eigh(const void* G, int32_t n, int32_t f64, void* work, void* evals, void* evecs, float tol,
+                       int32_t max_sweeps, int32_t* sweeps_out, void* stream);
 
 #ifdef __cplusplus
 }

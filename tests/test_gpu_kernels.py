@@ -390,6 +390,35 @@ def test_solve_rows_and_cholesky_vs_torch(lib):
     np.testing.assert_allclose(L.cpu().numpy(), torch.linalg.cholesky(G).cpu().numpy(), rtol=1e-9, atol=1e-9)
 
 
+def test_cholesky_reports_non_positive_pivot(lib):
+    G = torch.eye(64, device=DEV, dtype=torch.float64)
+    G[40, 40] = -1.0
+    info = torch.zeros(1, dtype=torch.int32, device=DEV)
+    _native.check(lib.dapb_cholesky(G.data_ptr(), 64, 1, info.data_ptr(), _native.stream_ptr()))
+    assert int(info.item()) == 41
+
+
+@pytest.mark.parametrize("n,dt,rows", [(512, torch.float32, 4096), (256, torch.float32, 300), (64, torch.float64, 500),
+                                       (24, torch.float64, 100), (128, torch.float32, 100)])
+def test_eigh_block_jacobi_vs_torch_fp64(dist, n, dt, rows):
+    """Native symmetric eigen-solver (csrc/dense_small.cu) against fp64 torch.linalg.eigh; rows < n gives a
+    rank-deficient Gram matrix (zero eigenvalues)."""
+    from distributed_algorithm_pyspark_b200.models.matrix_decomposition import GramDecomposition
+    torch.manual_seed(n + rows)
+    A = torch.randn(rows, n, device=DEV, dtype=torch.float64)
+    G = (A.T @ A).to(dt).contiguous()
+    dec = GramDecomposition(A.to(torch.bfloat16), dist, backend="fused", use_tc=False)
+    w, V = dec.eigh(G)
+    assert w.dtype == dt and 1 <= int(dec.sweeps.item()) <= 20
+    wr, _ = torch.linalg.eigh(G.double())
+    scale = float(wr.abs().max())
+    tol = 1e-6 if dt == torch.float32 else 1e-11
+    assert float((w.double() - wr).abs().max()) / scale < tol
+    Vd = V.double()
+    assert float((Vd.T @ Vd - torch.eye(n, device=DEV, dtype=torch.float64)).abs().max()) < (1e-3 if dt == torch.float32 else 1e-10)
+    assert float((Vd @ torch.diag(w.double()) @ Vd.T - G.double()).abs().max()) / scale < (2e-4 if dt == torch.float32 else 1e-10)
+
+
 def test_als_fused_matches_oracle(dist):
     from distributed_algorithm_pyspark_b200.models.matrix_decomposition import run_als
     cfg = ALSConfig(seed=0)
