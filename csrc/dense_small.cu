@@ -29,13 +29,55 @@ namespace {
 // ================================================================================================ Cholesky
 constexpr int kPb = 32;            // panel width = warp size
 
+// The 32 x 32 diagonal block is factored by ONE warp with the block in registers (row per lane).  Every index must be
+// a compile-time constant or the row array lands in local memory (measured: 25 us per block), and nvcc does not unroll
+// a 32 x 31 loop nest on request -- template recursion forces it.  Step J: pivot, scale column J, rank-1 update of the
+// columns right of it; the column entries travel by shuffles.
+// 1 / sqrt(d) and sqrt(d): fp32 takes the SFU estimate plus one Newton step (relative error ~1e-7) instead of the
+// IEEE sqrt + divide sequences, which sat on the critical path of every one of the 32 dependent steps.
+__device__ __forceinline__ void inv_sqrt(float d, float& sd, float& inv) {
+  float r = rsqrtf(d);
+  r = r * (1.5f - 0.5f * d * r * r);
+  inv = r; sd = d * r;
+}
+__device__ __forceinline__ void inv_sqrt(double d, double& sd, double& inv) { sd = sqrt(d); inv = 1.0 / sd; }
+
+template <typename T, int J>
+struct CholStep {
+  static __device__ __forceinline__ void run(T (&a)[kPb], int lane, int w, int& bad) {
+    T d = __shfl_sync(0xffffffffu, a[J], J);
+    if (J < w && !(d > (T)0)) { if (!bad) bad = J + 1; d = (T)1; }
+    T sd, inv;
+    inv_sqrt(d, sd, inv);
+    if (lane == J) a[J] = sd;
+    else if (lane > J) a[J] = a[J] * inv;
+#pragma unroll
+    for (int c = J + 1; c < kPb; ++c) {
+      const T lcj = __shfl_sync(0xffffffffu, a[J], c);       // L[c][J]
+      if (lane >= c) a[c] -= a[J] * lcj;
+    }
+    if constexpr (J + 1 < kPb) CholStep<T, J + 1>::run(a, lane, w, bad);
+  }
+};
+// Forward substitution of one panel row against L11 (shared memory, broadcast reads), same trick.
+template <typename T, int CC>
+struct SolveStep {
+  static __device__ __forceinline__ void run(T (&x)[kPb], const T (*L)[kPb + 1], const T* invd) {
+    T s = x[CC];
+#pragma unroll
+    for (int k = 0; k < CC; ++k) s -= x[k] * L[CC][k];
+    x[CC] = s * invd[CC];
+    if constexpr (CC + 1 < kPb) SolveStep<T, CC + 1>::run(x, L, invd);
+  }
+};
+
 // Shared-memory layout of the Cholesky kernel (dynamic: the fp64 variant exceeds the 48 KB static limit).
 template <typename T>
 struct CholSmem {
   T L11[kPb][kPb + 1];
+  T invd[kPb];             // 1 / L11[c][c]
   T Li[kPb][kPb + 1];
   T Lj[kPb][kPb + 1];
-  T X[256][kPb + 1];       // one panel row per thread for the triangular solve
 };
 
 template <typename T>
@@ -52,46 +94,37 @@ __global__ void __launch_bounds__(256) chol_coop_kernel(T* __restrict__ A, int n
     long long c0 = prof ? clock64() : 0;
     // ---- diagonal block: every CTA factors its own copy in shared memory (redundant, but no grid barrier needed
     //      before the panel solve); rows / columns beyond w act as an identity block ----
-    for (int i = tid; i < kPb * kPb; i += blockDim.x) {
-      const int r = i >> 5, c = i & 31;
-      sm.L11[r][c] = (r < w && c < w) ? (c <= r ? A[(int64_t)(j0 + r) * n + j0 + c] : (T)0) : (r == c ? (T)1 : (T)0);
-    }
-    __syncthreads();
-    if (warp == 0) {                                          // lane = row; all indexing is into shared memory
+    if (warp == 0) {
+      T a[kPb];
+#pragma unroll
+      for (int c = 0; c < kPb; ++c)
+        a[c] = (lane < w && c < w) ? (c <= lane ? A[(int64_t)(j0 + lane) * n + j0 + c] : (T)0) : (lane == c ? (T)1 : (T)0);
       int bad = 0;
-      for (int j = 0; j < kPb; ++j) {
-        T d = sm.L11[j][j];
-        if (j < w && !(d > (T)0)) { if (!bad) bad = j + 1; d = (T)1; }
-        const T sd = sqrt(d);
-        const T lrj = lane > j ? sm.L11[lane][j] / sd : (T)0;
-        __syncwarp();
-        if (lane == j) sm.L11[j][j] = sd;
-        else if (lane > j) sm.L11[lane][j] = lrj;
-        __syncwarp();
-        for (int c = j + 1; c < kPb; ++c) {
-          const T lcj = sm.L11[c][j];                          // broadcast
-          if (lane >= c) sm.L11[lane][c] -= lrj * lcj;
-        }
-        __syncwarp();
-      }
+      CholStep<T, 0>::run(a, lane, w, bad);
+#pragma unroll
+      for (int c = 0; c < kPb; ++c) sm.L11[lane][c] = a[c];
+      T dg = a[0];
+#pragma unroll
+      for (int c = 1; c < kPb; ++c) dg = lane == c ? a[c] : dg;
+      sm.invd[lane] = (T)1 / dg;
       if (blockIdx.x == 0) {
         if (bad && lane == 0 && *info == 0) *info = j0 + bad;
-        if (lane < w)
-          for (int c = 0; c <= lane && c < w; ++c) A[(int64_t)(j0 + lane) * n + j0 + c] = sm.L11[lane][c];
+#pragma unroll
+        for (int c = 0; c < kPb; ++c)
+          if (lane < w && c <= lane && c < w) A[(int64_t)(j0 + lane) * n + j0 + c] = a[c];
       }
     }
     __syncthreads();
     if (prof) { const long long c = clock64(); t_fac += c - c0; c0 = c; }
     // ---- rows below the block: solve X L11^T = A21, one thread per row, rows dealt over the whole grid ----
     for (int r = j0 + w + gtid; r < n; r += gth) {
-      T* x = sm.X[tid];
-      for (int cc = 0; cc < w; ++cc) x[cc] = A[(int64_t)r * n + j0 + cc];
-      for (int cc = 0; cc < w; ++cc) {
-        T s = x[cc];
-        for (int k = 0; k < cc; ++k) s -= x[k] * sm.L11[cc][k];
-        x[cc] = s / sm.L11[cc][cc];
-      }
-      for (int cc = 0; cc < w; ++cc) A[(int64_t)r * n + j0 + cc] = x[cc];
+      T x[kPb];
+#pragma unroll
+      for (int cc = 0; cc < kPb; ++cc) x[cc] = cc < w ? A[(int64_t)r * n + j0 + cc] : (T)0;
+      SolveStep<T, 0>::run(x, sm.L11, sm.invd);
+#pragma unroll
+      for (int cc = 0; cc < kPb; ++cc)
+        if (cc < w) A[(int64_t)r * n + j0 + cc] = x[cc];
     }
     if (prof) { const long long c = clock64(); t_sol += c - c0; c0 = c; }
     __threadfence();

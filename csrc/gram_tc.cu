@@ -12,10 +12,11 @@
 //
 // SYRK schedule.  G is symmetric, so only the 128 x 128 blocks (i, j) with i <= j are computed -- 10 of 16 for
 // P = 512 -- and off-diagonal blocks are written twice by the epilogue (as is and transposed).  The blocks are dealt
-// to ROLES of equal work (two blocks each for P = 512: {00,01} {02,03} {11,12} {13,22} {23,33}); a CTA is (role,
+// to ROLES of equal work (P = 512: six roles of one M128 x N256 MMA chain each, see make_roles); a CTA is (role,
 // row split), loads only the column strips its blocks touch (2 or 3 of 4), and keeps its <= 2 accumulators
 // (128 lanes x 256 columns) in TMEM for the whole kernel, so there is ONE epilogue: TMEM -> red.global.add into G.
-// All roles of a row split walk the same rows at the same pace, so HBM sees every row once (L2 serves the rest).
+// All roles of a row split cost the same per stage, walk the same rows at the same pace, and so HBM sees every row
+// once (L2 serves the other roles).
 //
 // Cross-GPU reduction (world > 1), same launch, whole grid: the row-split atomics go into a G-sized buffer in the
 // symmetric heap; after a grid barrier + rank barrier every rank reduces ITS 1/W slice of G over all ranks
@@ -37,7 +38,7 @@ namespace cg = cooperative_groups;
 constexpr int kKR = 64;            // rows per pipeline stage
 constexpr int kStages = 4;
 constexpr int kGThreads = 256;     // warp 0 TMA, warp 1 MMA, warp 2 TMEM alloc, warps 4-7 epilogue
-constexpr int kMaxRoles = 5;
+constexpr int kMaxRoles = 6;
 
 // One role = up to two MMA groups on up to three loaded column strips (see the schedule above).
 struct GramRole {
@@ -48,7 +49,8 @@ struct GramRole {
   int n[2];                // N of the group's MMA: 128 or 256
   int tmem_col[2];         // accumulator column of the group
   int n_out;               // 128 x 128 output blocks
-  int out_i[2], out_j[2];  // block coordinates (strip units), block k sits at TMEM column 128 * k
+  int out_i[2], out_j[2];  // block coordinates (strip units)
+  int out_col[2];          // TMEM column of output block k
 };
 
 struct GramTcArgs {
@@ -66,15 +68,20 @@ struct GramTcArgs {
   int* progress;          // [splits][kMaxRoles] stage counters of the pacing protocol (zeroed by the host wrapper)
   int pace_every, pace_window;
   int prefetch;           // L2 prefetch distance in stages (0 = off)
+  int dbg;                // DAPB_GRAM_DBG=1: per-CTA cycle counters into progress[512 + 4 * blockIdx.x ..] (>> 10)
   GramRole roles[kMaxRoles];
 };
 
-// Pacing.  The roles of one row split read the SAME rows; HBM serves a row once only while they stay close enough
-// together for L2 to hold it.  Nothing couples them by itself (a role that loads three strips per stage is slower than
-// one that loads two, and the lead grows over the whole kernel), so every kPaceEvery stages a producer publishes its
-// stage counter and waits until the slowest role of its split is within kPaceWindow stages.  The window of all splits
-// together (29 x 16 x 64 KB = 30 MB) is a fraction of the 126 MB L2.  All CTAs are resident (cooperative launch).
-constexpr int kPaceEvery = 16;     // defaults; DAPB_GRAM_PACE_EVERY (0 = no pacing) / DAPB_GRAM_PACE_WINDOW override
+// Optional pacing / L2 prefetch (both OFF by default -- measured, they do not pay):
+//  * pacing: every pace_every stages a producer publishes its stage counter and waits until the slowest role of its row
+//    split is within pace_window stages, so that the roles of a split keep hitting each other's rows in L2;
+//  * prefetch: role 0 of every split issues cp.async.bulk.prefetch.tensor.L2 `prefetch` stages ahead, full width.
+// With the six equal-cost roles of make_roles the roles stay in lockstep by themselves (cycle counters: 9.961 / 9.965 /
+// 9.961 / 9.965 / 9.961 M cycles per role) and the kernel is bound by the tensor core's MN-major operand reads (an
+// M128 x N256 x K16 MMA measures 201 cycles against a 128-cycle floor), not by DRAM: pacing on cost +40 %, the prefetch
+// instructions slowed role 0's producer (+48 % on that role).  DAPB_GRAM_PACE_EVERY / _WINDOW / DAPB_GRAM_PREFETCH switch
+// them on for experiments; profiles/gram_tc_roles_r2.jsonl and profiles/ncu_gram_tc_syrk_r2.md hold the measurements.
+constexpr int kPaceEvery = 0;      // defaults (0 = off); DAPB_GRAM_PACE_EVERY / DAPB_GRAM_PACE_WINDOW override
 constexpr int kPaceWindow = 32;
 __device__ __forceinline__ void pace_store(int* p, int v) {
   asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
@@ -139,11 +146,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             __nanosleep(200);
           }
         }
-        // Role 0 of every row split runs an L2 prefetch kPrefetch stages ahead of the shared-memory ring, full width.
-        // The ring alone keeps splits x kStages x 64 KB = 7 MB of DISTINCT bytes in flight (all roles of a split read
-        // the same rows), which at ~2 us of DRAM latency caps HBM at ~3.7 TB/s (ncu: 49 % DRAM, 47 % tensor, both
-        // starved); the prefetch window (29 x 16 x 64 KB = 30 MB, a quarter of L2) lifts that cap, and every role's
-        // TMA load then finds its rows in L2, so HBM serves each row once.
+        // optional L2 prefetch by role 0 (off by default, see above)
         if (role_id == 0 && a.prefetch > 0 && t + a.prefetch < t_end) {
           for (int b = 0; b < P / 64; ++b) tma_prefetch_2d(&map_a, b * 64, (int)((t + a.prefetch) * kKR));
         }
@@ -163,9 +166,12 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       const uint32_t idesc1 = make_idesc_bf16(128, role.n_groups > 1 ? role.n[1] : 128, 1, 1);
       const uint64_t tmpl = make_smem_desc_sw128(0, box_bytes, 1024);  // LBO = next 64-column box, SBO = next 8 rows
       uint32_t it = 0;
+      long long w_full = 0;
+      const long long t_mma0 = clock64();
       for (int64_t t = t_begin; t < t_end; ++t, ++it) {
         const uint32_t st = it % kStages;
-        mbar_wait(&full[st], (it / kStages) & 1);
+        if (a.dbg) { const long long c0 = clock64(); mbar_wait(&full[st], (it / kStages) & 1); w_full += clock64() - c0; }
+        else mbar_wait(&full[st], (it / kStages) & 1);
         tc_fence_after();
         const uint32_t base = smem_u32(smem + st * stage_bytes);
 #pragma unroll
@@ -181,6 +187,10 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         umma_commit(&empty[st]);
       }
       umma_commit(acc_done);
+      if (a.dbg) {
+        int* d = a.progress + 512 + 4 * blockIdx.x;
+        d[0] = role_id; d[1] = (int)((clock64() - t_mma0) >> 10); d[2] = (int)(w_full >> 10);
+      }
     }
   } else if (warp >= 4) {
     // ===================== epilogue: TMEM blocks -> atomics into G (and the mirrored block) =====================
@@ -196,7 +206,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         float* gcol = a.G_acc + (size_t)(bj * 128) * P + gi;  // mirrored element (j, gi): lanes hit consecutive addresses
         for (int j0 = 0; j0 < 128; j0 += 32) {
           uint32_t v[32];
-          tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(qd * 32) << 16) + k * 128 + j0, v);
+          tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(qd * 32) << 16) + role.out_col[k] + j0, v);
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 32; j += 4)
@@ -240,23 +250,9 @@ int make_roles(int S, GramRole* r) {
   memset(r, 0, sizeof(GramRole) * kMaxRoles);
   auto pair256 = [](GramRole& q, int i, int j0) {            // blocks (i, j0), (i, j0 + 1) as ONE N = 256 MMA
     q.n_groups = 1; q.n[0] = 256; q.tmem_col[0] = 0;
-    q.n_out = 2; q.out_i[0] = q.out_i[1] = i; q.out_j[0] = j0; q.out_j[1] = j0 + 1;
+    q.n_out = 2; q.out_i[0] = q.out_i[1] = i; q.out_j[0] = j0; q.out_j[1] = j0 + 1; q.out_col[0] = 0; q.out_col[1] = 128;
     if (j0 == i) { q.n_strips = 2; q.strips[0] = i; q.strips[1] = i + 1; q.a_pos[0] = 0; q.b_pos[0] = 0; }
     else { q.n_strips = 3; q.strips[0] = i; q.strips[1] = j0; q.strips[2] = j0 + 1; q.a_pos[0] = 0; q.b_pos[0] = 1; }
-  };
-  auto two128 = [](GramRole& q, int i0, int j0, int i1, int j1) {   // two independent 128 x 128 blocks
-    int st[4] = {i0, j0, i1, j1}, ns = 0;
-    for (int s = 0; s < 4; ++s) {                            // sorted unique strips
-      bool seen = false;
-      for (int t = 0; t < ns; ++t) seen |= q.strips[t] == st[s];
-      if (!seen) q.strips[ns++] = st[s];
-    }
-    for (int x = 0; x < ns; ++x) for (int y = x + 1; y < ns; ++y) if (q.strips[y] < q.strips[x]) { int t = q.strips[x]; q.strips[x] = q.strips[y]; q.strips[y] = t; }
-    q.n_strips = ns;
-    auto pos = [&](int s) { for (int t = 0; t < ns; ++t) if (q.strips[t] == s) return t; return 0; };
-    q.n_groups = 2; q.n[0] = q.n[1] = 128; q.tmem_col[0] = 0; q.tmem_col[1] = 128;
-    q.a_pos[0] = pos(i0); q.b_pos[0] = pos(j0); q.a_pos[1] = pos(i1); q.b_pos[1] = pos(j1);
-    q.n_out = 2; q.out_i[0] = i0; q.out_j[0] = j0; q.out_i[1] = i1; q.out_j[1] = j1;
   };
   if (S == 1) {
     r[0].n_strips = 1; r[0].strips[0] = 0; r[0].n_groups = 1; r[0].n[0] = 128; r[0].n_out = 1;
@@ -267,12 +263,30 @@ int make_roles(int S, GramRole* r) {
     r[1].n_strips = 1; r[1].strips[0] = 1; r[1].n_groups = 1; r[1].n[0] = 128; r[1].n_out = 1; r[1].out_i[0] = r[1].out_j[0] = 1;
     return 2;
   }
-  pair256(r[0], 0, 0);             // 00 01
-  pair256(r[1], 0, 2);             // 02 03
-  pair256(r[2], 1, 1);             // 11 12
-  two128(r[3], 1, 3, 2, 2);        // 13 22
-  two128(r[4], 2, 3, 3, 3);        // 23 33
-  return 5;
+  // P = 512.  Measured (per-role cycle counters, profiles/gram_tc_roles_r2.jsonl): MN-major operand reads make an
+  // M128 x N256 MMA cost ~200 cycles and an M128 x N128 one ~170, so a role built from two N = 128 MMAs is 1.6x slower
+  // than one N = 256 MMA covering the same two blocks.  The 10 blocks cannot be tiled exactly by (strip, adjacent strip
+  // pair) products, so six N = 256 roles are used and two of their twelve blocks (12 and 23, computed twice) are simply
+  // not written by the duplicate: 12 block products instead of the 16 of the full matrix, all roles equally fast.
+  auto strip_pair = [](GramRole& q, int a_strip, int b0, bool write0, bool write1) {    // A = a_strip, B = strips b0, b0 + 1
+    q.n_groups = 1; q.n[0] = 256; q.tmem_col[0] = 0;
+    if (a_strip == b0) { q.n_strips = 2; q.strips[0] = b0; q.strips[1] = b0 + 1; q.a_pos[0] = 0; q.b_pos[0] = 0; }
+    else if (a_strip == b0 + 1) { q.n_strips = 2; q.strips[0] = b0; q.strips[1] = b0 + 1; q.a_pos[0] = 1; q.b_pos[0] = 0; }
+    else if (a_strip < b0) { q.n_strips = 3; q.strips[0] = a_strip; q.strips[1] = b0; q.strips[2] = b0 + 1; q.a_pos[0] = 0; q.b_pos[0] = 1; }
+    else { q.n_strips = 3; q.strips[0] = b0; q.strips[1] = b0 + 1; q.strips[2] = a_strip; q.a_pos[0] = 2; q.b_pos[0] = 0; }
+    q.n_out = 0;
+    for (int t = 0; t < 2; ++t) {
+      if (!(t == 0 ? write0 : write1)) continue;
+      q.out_i[q.n_out] = a_strip; q.out_j[q.n_out] = b0 + t; q.out_col[q.n_out] = 128 * t; ++q.n_out;
+    }
+  };
+  strip_pair(r[0], 0, 0, true, true);      // 00 01
+  strip_pair(r[1], 0, 2, true, true);      // 02 03
+  strip_pair(r[2], 1, 1, true, true);      // 11 12
+  strip_pair(r[3], 1, 2, false, true);     // (12) 13
+  strip_pair(r[4], 2, 2, true, true);      // 22 23
+  strip_pair(r[5], 3, 2, false, true);     // (32) 33
+  return 6;
 }
 
 }  // namespace
@@ -323,8 +337,10 @@ extern "C" int dapb_gram_tc(const DapbComm* comm, const void* A, int64_t n_rows,
     static const int pe = getenv("DAPB_GRAM_PACE_EVERY") ? atoi(getenv("DAPB_GRAM_PACE_EVERY")) : kPaceEvery;
     static const int pw = getenv("DAPB_GRAM_PACE_WINDOW") ? atoi(getenv("DAPB_GRAM_PACE_WINDOW")) : kPaceWindow;
     a.pace_every = pe; a.pace_window = pw;
-    static const int pf = getenv("DAPB_GRAM_PREFETCH") ? atoi(getenv("DAPB_GRAM_PREFETCH")) : 16;
+    static const int pf = getenv("DAPB_GRAM_PREFETCH") ? atoi(getenv("DAPB_GRAM_PREFETCH")) : 0;
     a.prefetch = pf;
+    static const int dg = getenv("DAPB_GRAM_DBG") ? atoi(getenv("DAPB_GRAM_DBG")) : 0;
+    a.dbg = dg;
   }
   DAPB_CUDA_CHECK(cudaMemsetAsync(tickets, 0, (size_t)DAPB_GRAM_TC_SCRATCH_WORDS * sizeof(uint32_t), st));
   const uint32_t smem = kStages * 3 * 2 * kKR * 128 + 128 + 1024;

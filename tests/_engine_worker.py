@@ -174,6 +174,20 @@ def main():
     Gr = A.T @ A
     dist.all_reduce_sum(Gr)
     out["gram_rel_diff"] = float((G - Gr).abs().max().item() / Gr.abs().max().item())
+    # ---- tensor-core Gram (SYRK roles) with the grid-wide in-kernel two-shot all-reduce, twice (epoch / buffer reuse)
+    from distributed_algorithm_pyspark_b200.ops.gram_tc import GramTC
+    out["gram_tc_rel_diff"] = []
+    for Pn in (256, 512):
+        At = (torch.randn(6000 + 100 * dist.rank, Pn, device=dev)).to(torch.bfloat16).contiguous()
+        tc = GramTC(At, dist, heap=heap)
+        ref_g = At.float().T @ At.float()
+        dist.all_reduce_sum(ref_g)
+        for _ in range(2):
+            Gt = tc().clone()
+            gs = dist.all_gather(Gt)
+            out["gram_tc_rel_diff"].append(float((Gt - ref_g).abs().max().item() / ref_g.abs().max().item()))
+            out.setdefault("gram_tc_identical_across_ranks", True)
+            out["gram_tc_identical_across_ranks"] = out["gram_tc_identical_across_ranks"] and all(bool(torch.equal(gs[0], t)) for t in gs)
     if dist.is_main:
         with open(out_path, "w") as f:
             json.dump(out, f)

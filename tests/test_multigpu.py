@@ -82,4 +82,5 @@ def test_engines_fused_vs_nccl_multi_gpu(tmp_path):
     assert out["kmeans_big_counts_exact"]
     assert out["pagerank_rel_diff"] < 1e-3
     assert out["gram_rel_diff"] < 1e-4
+    assert max(out["gram_tc_rel_diff"]) < 1e-4 and out["gram_tc_identical_across_ranks"], out["gram_tc_rel_diff"]
     assert out["tc"] == [[337025, 18]] * 3, out["tc"]          # oracle: 337025 pairs after 18 rounds
