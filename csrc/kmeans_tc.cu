@@ -82,7 +82,8 @@ struct SmemLayout {
 };
 
 struct KmTcArgs {
-  const __nv_bfloat16* X; // [n, KD]
+  const __nv_bfloat16* X; // [n, KD] bf16 points: tensor-core operand (and source of the sums unless X32 is set)
+  const float* X32;       // optional [n, KD] fp32 originals: the per-cluster sums are taken from these
   int64_t n;              // rows
   int k;                  // centroids incl. padding (multiple of 128, <= 16384)
   const float* cnorm;     // [k + 8 + 8 k]: biased norms, 8 aux words, then the K = 16 norm slabs (see kmeans_norm_slab)
@@ -391,6 +392,38 @@ kmeans_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         const bool lane_on = lane * 4 < KD || kP > 1;
         // batches of 8 rows: all loads of a batch are issued before the first atomic, so one L2 round trip is
         // paid per batch instead of per row
+        if (a.X32 != nullptr) {
+          // fp32 points: the bf16 shadow copy decided the assignment, the sums are accumulated from the ORIGINAL rows
+          // (ref k-means.py:62-63 sums the points themselves), 16 bytes per lane per row
+          for (int i0 = 0; i0 < n_rows; i0 += 8) {
+            float4 raw4[8][kP];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              const float* xr = a.X32 + (row_base + min(i0 + u, n_rows - 1)) * (int64_t)KD;
+#pragma unroll
+              for (int p = 0; p < kP; ++p) {
+                const int col = p * 128 + lane * 4;
+                raw4[u][p] = (col < KD) ? __ldg(reinterpret_cast<const float4*>(xr + col)) : make_float4(0.f, 0.f, 0.f, 0.f);
+              }
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              const int cidx = __shfl_sync(0xffffffffu, my_c, min(i0 + u, 31));
+              if (i0 + u < n_rows && lane_on) {
+#pragma unroll
+                for (int p = 0; p < kP; ++p) {
+                  const int col = p * 128 + lane * 4;
+                  if (col < KD) {
+                    float* dst = a.sums + (size_t)cidx * KD + col;
+                    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "f"(raw4[u][p].x), "f"(raw4[u][p].y),
+                                 "f"(raw4[u][p].z), "f"(raw4[u][p].w) : "memory");
+                  }
+                }
+              }
+            }
+          }
+          continue;
+        }
         for (int i0 = 0; i0 < n_rows; i0 += 8) {
           uint2 raw[8][kP];
 #pragma unroll
@@ -518,9 +551,26 @@ extern "C" int dapb_kmeans_assign_tc(const void* X, int64_t n, int32_t d, const 
 // Same, with an optional device buffer of 64 int64 cycle counters filled by CTA 0 (per-role wait times):
 // [role*8 + i], roles 0 X-producer, 1 MMA issuer, 3 centroid-producer, 4 arg-min warp, 5 scatter warp;
 // i = 0..2 wait counters, 3 MMA issue, 5 commits, 4 = total cycles.  Used by scripts/kmeans_tc_probe.py.
+static int kmeans_assign_tc_impl(const void* X, const float* X32, int64_t n, int32_t d, const void* b_operand,
+                                 const float* cnorm, int32_t k, int32_t* assign, float* sums,
+                                 int32_t* counts, int32_t grid, long long* dbg, void* stream);
 extern "C" int dapb_kmeans_assign_tc_dbg(const void* X, int64_t n, int32_t d, const void* b_operand,
                                          const float* cnorm, int32_t k, int32_t* assign, float* sums,
                                          int32_t* counts, int32_t grid, long long* dbg, void* stream) {
+  return kmeans_assign_tc_impl(X, nullptr, n, d, b_operand, cnorm, k, assign, sums, counts, grid, dbg, stream);
+}
+// fp32 points on the tensor-core path: X_bf16 is a bf16 copy of X32 (same shape) that feeds the distance MMAs, X32 the
+// original rows from which the per-cluster sums are accumulated.  Assignments are nearest centroids of the ROUNDED
+// points (they differ from the fp32 arg-min only on near-ties below bf16 resolution).
+extern "C" int dapb_kmeans_assign_tc_f32(const void* X_bf16, const float* X32, int64_t n, int32_t d, const void* b_operand,
+                                         const float* cnorm, int32_t k, int32_t* assign, float* sums,
+                                         int32_t* counts, int32_t grid, void* stream) {
+  DAPB_REQUIRE(X32 != nullptr && (reinterpret_cast<uintptr_t>(X32) & 15) == 0, "kmeans_assign_tc_f32: X32 must be 16-byte aligned");
+  return kmeans_assign_tc_impl(X_bf16, X32, n, d, b_operand, cnorm, k, assign, sums, counts, grid, nullptr, stream);
+}
+static int kmeans_assign_tc_impl(const void* X, const float* X32, int64_t n, int32_t d, const void* b_operand,
+                                 const float* cnorm, int32_t k, int32_t* assign, float* sums,
+                                 int32_t* counts, int32_t grid, long long* dbg, void* stream) {
   DAPB_REQUIRE(X && b_operand && cnorm && sums && counts, "kmeans_assign_tc: null argument");
   DAPB_REQUIRE(d == 64 || d == 128, "kmeans_assign_tc: d must be 64 or 128 (got %d)", d);
   DAPB_REQUIRE(k >= 1 && k <= 16384, "kmeans_assign_tc: k must be in [1, 16384] (got %d)", k);
@@ -531,7 +581,7 @@ extern "C" int dapb_kmeans_assign_tc_dbg(const void* X, int64_t n, int32_t d, co
   if (rc) return rc;
   rc = make_tensor_map_bf16_2d(&mc, b_operand, (uint64_t)k, (uint64_t)d, (uint64_t)d, 64, kNB);
   if (rc) return rc;
-  KmTcArgs a{(const __nv_bfloat16*)X, n, k, cnorm, sums, counts, assign, dbg, 0, 32u};
+  KmTcArgs a{(const __nv_bfloat16*)X, X32, n, k, cnorm, sums, counts, assign, dbg, 0, 32u};
   if (grid <= 0) grid = dapb::sm_count();
   const int64_t n_super = ((n + kTM - 1) / kTM + kSuper - 1) / kSuper;
   if (grid > n_super) grid = (int)n_super;

@@ -161,7 +161,9 @@ __global__ void __launch_bounds__(kPrThreads) pagerank_step_kernel(PrArgs a, Dap
 // =================================================================================================
 constexpr int kWarpCap = 512;
 constexpr int kWarpsPerCta = kPrThreads / 32;
-constexpr int kGrab = 4;             // work items per atomic
+constexpr int kGrabDefault = 1;      // work items per atomic (DAPB_PR_GRAB overrides): an item keeps a warp busy for tens of
+                                     // microseconds once 48 warps share an SM's gather bandwidth, so the end-of-iteration tail is
+                                     // one GRAB long -- 4 items per grab cost ~50 us of every 290 us iteration at 8 GPUs
 constexpr int kHubDeep = 16;         // measured: 8 -> 16 gathers in flight per lane +5..8 %, 32 no better
 
 template <typename VT>
@@ -182,6 +184,7 @@ struct PrRunArgs {
   int32_t wait_first;       // wait for epoch0 - 1 before the first iteration (0 right after init + host barrier)
   int32_t skip_empty_ok;
   uint32_t* sync;           // [4] ticket, work counter parity 0 / 1, pad -- zero at launch
+  int32_t grab;             // work items taken per atomic
   unsigned long long* stats;  // optional [n_iters][4] globaltimer stamps: enter, wait passed, last ticket, published
   // hub rows
   const int32_t* hub_rows; const int32_t* hub_col; const int64_t* chunk_start; const int64_t* chunk_end;
@@ -274,10 +277,10 @@ __global__ void __launch_bounds__(kPrThreads, sizeof(VT) == 4 ? 6 : 4) pagerank_
 
     for (;;) {
       int first = 0;
-      if (lane == 0) first = (int)atomicAdd(work, (uint32_t)kGrab);
+      if (lane == 0) first = (int)atomicAdd(work, (uint32_t)a.grab);
       first = __shfl_sync(0xffffffffu, first, 0);
       if (first >= n_items) break;
-      const int last = min(first + kGrab, n_items);
+      const int last = min(first + a.grab, n_items);
       for (int item = first; item < last; ++item) {
         if (item < a.n_chunks) {
           // ---- one chunk of a hub row ----
@@ -439,7 +442,8 @@ int pagerank_run_impl(const DapbPrRunArgs& r, const DapbComm& c, cudaStream_t st
   int grid = per_sm * dapb::sm_count();                 // every CTA must be resident: they wait for each other's flag
   if (r.grid > 0 && r.grid < grid) grid = r.grid;
   const int64_t items = (int64_t)a.n_chunks + a.n_blocks;
-  const int64_t need = (items + kWarpsPerCta * kGrab - 1) / (kWarpsPerCta * kGrab);
+  { static const int g_env = getenv("DAPB_PR_GRAB") ? atoi(getenv("DAPB_PR_GRAB")) : kGrabDefault; a.grab = g_env > 0 ? g_env : 1; }
+  const int64_t need = (items + kWarpsPerCta * a.grab - 1) / (kWarpsPerCta * a.grab);
   if (grid > need) grid = need > 0 ? (int)need : 1;
   DAPB_CUDA_CHECK(cudaMemsetAsync(a.sync, 0, 4 * sizeof(uint32_t), st));
   DapbComm cc = c;

@@ -121,6 +121,7 @@ def _declare(lib: C.CDLL):
         "dapb_kmeans_payload_bytes": (u64, [i32, i32, i32, i32]),
         "dapb_kmeans_tc_prepare": (C.c_int, [vp, i32, i32, vp, vp, C.c_float, vp]),
         "dapb_kmeans_assign_tc": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, vp, vp, i32, vp]),
+        "dapb_kmeans_assign_tc_f32": (C.c_int, [vp, vp, i64, i32, vp, vp, i32, vp, vp, vp, i32, vp]),
         "dapb_kmeans_assign_tc_dbg": (C.c_int, [vp, i64, i32, vp, vp, i32, vp, vp, vp, i32, vp, vp]),
         "dapb_pagerank_init": (C.c_int, [P(DapbComm), vp, i64, i64, i64, f64, u64, i32, vp]),
         "dapb_pagerank_step": (C.c_int, [P(DapbComm), vp, vp, vp, vp, i32, i64, i64, i64, f32, f32, vp,

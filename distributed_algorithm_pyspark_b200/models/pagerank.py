@@ -150,8 +150,9 @@ def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Opti
     dist = dist or current()
     if layout is None:                  # "warp": warp-granular kernel + hub rows (default); "cta": CTA-wide row blocks
         layout = os.environ.get("DAPB_PR_LAYOUT", "warp")
+    auto_block = block_nnz is None and layout == "warp" and os.environ.get("DAPB_PR_BLOCK_NNZ") is None
     if block_nnz is None:
-        block_nnz = 512 if layout == "warp" else 2048
+        block_nnz = int(os.environ.get("DAPB_PR_BLOCK_NNZ", 512)) if layout == "warp" else 2048
     if hub_threshold is None:
         hub_threshold = int(os.environ.get("DAPB_PR_HUB_THRESHOLD", 64))       # measured: 32..256 within 5 %, 64 best
     if hub_chunk is None:
@@ -188,6 +189,13 @@ def build_sharded_graph(src: torch.Tensor, dst: torch.Tensor, V: int, dist: Opti
     if layout == "warp":
         row_ptr, col_local, hub = split_hub_rows(row_ptr, col_local, hub_threshold, hub_chunk)
     nnz = int(row_ptr[-1].item())
+    if auto_block:
+        # A work item keeps a warp busy for tens of microseconds (48 warps share an SM's gather bandwidth), and the
+        # end-of-iteration tail of the persistent kernel is one item long: keep >= ~32 items per resident warp so the tail
+        # stays a few per cent of the iteration (measured at 2 ranks, scale 22: 512 -> 256 per item = -16 %)
+        warps = 148 * 6 * 8
+        per_warp = (nnz + nv) / warps
+        block_nnz = 512 if per_warp >= 512 * 32 else (256 if per_warp >= 256 * 32 else 128)
     cumw = (row_ptr[:-1] + torch.arange(nv, device=src.device, dtype=torch.int64)).contiguous()
     n_blocks = max(1, (nnz + nv + block_nnz - 1) // block_nnz)
     targets = torch.arange(n_blocks, device=src.device, dtype=torch.int64) * block_nnz

@@ -240,6 +240,10 @@ DAPB_API int dapb_kmeans_tc_prepare(const float* centers, int32_t k, int32_t d, 
 DAPB_API int dapb_kmeans_assign_tc(const void* X, int64_t n, int32_t d, const void* b_operand, const float* cnorm,
                                    int32_t k, int32_t* assign, float* sums, int32_t* counts, int32_t grid,
                                    void* stream);
+/* fp32 points on the same tensor-core kernel: X_bf16 = bf16 copy of X32 (feeds the MMAs), sums come from the fp32 rows. */
+DAPB_API int dapb_kmeans_assign_tc_f32(const void* X_bf16, const float* X32, int64_t n, int32_t d, const void* b_operand,
+                                       const float* cnorm, int32_t k, int32_t* assign, float* sums, int32_t* counts,
+                                       int32_t grid, void* stream);
 DAPB_API int dapb_kmeans_assign_tc_dbg(const void* X, int64_t n, int32_t d, const void* b_operand,
                                        const float* cnorm, int32_t k, int32_t* assign, float* sums,
                                        int32_t* counts, int32_t grid, long long* dbg, void* stream);

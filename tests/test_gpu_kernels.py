@@ -222,6 +222,24 @@ def test_kmeans_empty_cluster_and_tie(dist):
     np.testing.assert_array_equal(res.assignment, [0, 0])
 
 
+def test_kmeans_fp32_points_take_the_tensor_core_path(dist):
+    """fp32 points: bf16 shadow copy for the distance MMAs, sums from the fp32 rows -> centres match the fp32 baseline to
+    fp32 accuracy when the clusters are separated (assignments cannot differ)."""
+    from distributed_algorithm_pyspark_b200.models.kmeans import ShardedKMeans
+    torch.manual_seed(3)
+    true_c = torch.randn(256, 128, device=DEV) * 4
+    X = (true_c[torch.randint(0, 256, (30000,), device=DEV)] + 0.2 * torch.randn(30000, 128, device=DEV)).contiguous()
+    c0 = (true_c + 0.3 * torch.randn_like(true_c)).contiguous()
+    a = ShardedKMeans(X, 256, c0, dist=dist, backend="fused")
+    assert a.tc is not None and a.tc.X32 is not None
+    b = ShardedKMeans(X, 256, c0, dist=dist, backend="nccl")
+    for _ in range(3):
+        a.step(); b.step()
+    torch.cuda.synchronize()
+    assert torch.equal(a.counts_out, b.counts_out)
+    torch.testing.assert_close(a.centers, b.centers, rtol=1e-4, atol=1e-4)
+
+
 # ------------------------------------------------------------------------------------------ F4
 def test_pagerank_fused_toy_and_random_vs_oracle(dist):
     from distributed_algorithm_pyspark_b200.models.pagerank import run_pagerank
