@@ -71,7 +71,49 @@ def bench_kmeans(dist, backend, n=125_000_000, d=128, k=1024, iters=20, warmup=1
         bms = _timed(dist, base.step, 2, 1)
         out["kmeans_baseline_ms_per_iter"] = bms
         out["kmeans_vs_baseline"] = bms / ms
+        # lower bound for ANY cuBLAS-based formulation: just the two GEMMs an iteration needs (distances, one-hot sums),
+        # bf16 in / bf16 out, no elementwise work, no arg-min, no collective
+        CmT = c0.to(torch.bfloat16).T.contiguous()
+        chunk = 1 << 20
+        oh = torch.zeros(chunk, k, dtype=torch.bfloat16, device=dev)
+
+        def gemms_only():
+            for i in range(0, n, chunk):
+                x = X[i:i + chunk]
+                torch.mm(x, CmT)
+                torch.mm(oh[:x.shape[0]].T, x)
+        gms = _timed(dist, gemms_only, 1, 1)
+        out["kmeans_cublas_gemms_only_ms_per_iter"] = gms
+        out["kmeans_vs_cublas_gemms_only"] = gms / ms
+        del oh, CmT
         eng = base
+    del X, eng
+    torch.cuda.empty_cache()
+    return out
+
+
+def bench_kmeans_fp32(dist, n=125_000_000, d=128, k=1024, iters=5, warmup=1):
+    """Same shape with fp32 storage (64 GB per GPU): distances on the tensor cores from a bf16 shadow copy (+32 GB), sums
+    from the fp32 rows.  Roofline: max(tensor 2 n k d / sustained bf16, HBM (64 + 32 GB) / measured copy bandwidth)."""
+    import torch
+    from distributed_algorithm_pyspark_b200.data.datasets import synthetic_clusters_device
+    from distributed_algorithm_pyspark_b200.models.kmeans import ShardedKMeans
+    dev = dist.device
+    free, _ = torch.cuda.mem_get_info(dev)
+    while n * d * 6 > 0.7 * free:
+        n //= 2
+    X, centres = synthetic_clusters_device(n, d, k, dev, torch.float32, seed=7 + dist.rank)
+    c0 = (centres + 0.5 * torch.randn_like(centres)).float()
+    if dist.world > 1:
+        dist.broadcast(c0, 0)
+    eng = ShardedKMeans(X, k, c0, dist=dist, backend="fused")
+    ms = _timed(dist, eng.step, iters, warmup)
+    pk = _peaks()
+    t_tensor = 2.0 * n * k * d / (pk["bf16_tflops_sustained"] * 1e12) * 1e3
+    t_hbm = n * d * 6 / (pk["hbm_gbs"] * 1e9) * 1e3
+    out = {"kmeans_fp32_ms_per_iter": ms, "kmeans_fp32_n_per_gpu": n, "kmeans_fp32_pts_per_s_iter": n * dist.world / (ms / 1e3),
+           "kmeans_fp32_tensor_core_path": bool(eng.tc is not None and eng.tc.X32 is not None),
+           "kmeans_fp32_roofline_ms": max(t_tensor, t_hbm), "kmeans_fp32_frac_of_roofline": max(t_tensor, t_hbm) / ms}
     del X, eng
     torch.cuda.empty_cache()
     return out
@@ -314,6 +356,11 @@ def run_all(dist, backend, only=None, baseline=False, checks=None, **kw):
             out.update(fn(dist, backend, baseline=baseline, checks=checks, **kw.get(name, {})))
         except Exception as e:                          # one failing extra must not hide the others
             out[name + "_error"] = repr(e)[:300]
+    if (not only or "kmeans" in only) and backend == "fused":
+        try:    # fp32 points (SURVEY 7.4 sized k-means for fp32 storage): tensor-core path via a resident bf16 shadow copy
+            out.update(bench_kmeans_fp32(dist))
+        except Exception as e:
+            out["kmeans_fp32_error"] = repr(e)[:300]
     if (not only or "pagerank" in only) and backend == "fused" and not os.environ.get("DAPB_BENCH_SKIP_PR24"):
         try:    # continuity with round 1 (strong scaling of the smaller graph) + the N-GPU vs 1-GPU result check
             out.update(bench_pagerank(dist, backend, scale=24, iters=30, stats=False, tag="pagerank24"))

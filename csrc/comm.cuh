@@ -146,11 +146,13 @@ __device__ __forceinline__ uint64_t oneshot_bytes(int world, int n) {
   return (uint64_t)2 * world * ((n + 3) & ~3) * sizeof(T);
 }
 
+// `slot_stride` (elements, multiple of 4, >= n): distance between the ranks' slots; 0 = n rounded up to 4.  Callers that
+// send messages of different lengths through ONE region pass a fixed stride so that the two parity areas never overlap.
 template <typename T>
 __device__ void block_allreduce_oneshot(const DapbComm& c, int my_rank, uint64_t off,
                                         uint32_t flag_base, uint64_t epoch, const T* src,
-                                        T* dst, int n) {   // src may alias dst
-  const int n_pad = (n + 3) & ~3;
+                                        T* dst, int n, int slot_stride = 0) {   // src may alias dst
+  const int n_pad = slot_stride > 0 ? slot_stride : ((n + 3) & ~3);
   if (c.world == 1) {
     for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
     __syncthreads();

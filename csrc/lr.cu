@@ -359,7 +359,7 @@ __device__ void lr_finish_slice(const DapbLrStepArgs& a, const DapbComm& c, floa
       g_s[nc + 1] = (float)(cnt_local >> 16);
     }
     __syncthreads();
-    block_allreduce_oneshot<float>(c, c.rank, off, fb, a.epoch, g_s, g_s, nc + 2);
+    block_allreduce_oneshot<float>(c, c.rank, off, fb, a.epoch, g_s, g_s, nc + 2, cps + 4);
     if (a.stats && slice == 0 && tid == 0) a.stats[2] = global_timer_ns();
     const int cnt_i = (int)g_s[nc] + ((int)g_s[nc + 1] << 16);
     const float cnt_tot = (float)cnt_i;
@@ -398,7 +398,7 @@ __device__ void lr_finish_slice(const DapbLrStepArgs& a, const DapbComm& c, floa
   // model all-reduce fused with the MA average / BMUF filter / EASGD centre update
   // (ref ma.py:104-106, bmuf.py:109-114, easgd.py:104-106)
   float* sum_s = red;                      // nt * 4 >= cps floats for every supported block size
-  block_allreduce_oneshot<float>(c, c.rank, off, fb, a.epoch, g_s, sum_s, nc);
+  block_allreduce_oneshot<float>(c, c.rank, off, fb, a.epoch, g_s, sum_s, nc, cps + 4);
   if (a.stats && slice == 0 && tid == 0) a.stats[2] = global_timer_ns();
   const float invP = 1.f / (float)a.n_replicas_total;
   for (int d = tid; d < nc; d += nt) {

@@ -161,9 +161,8 @@ __global__ void __launch_bounds__(kPrThreads) pagerank_step_kernel(PrArgs a, Dap
 // =================================================================================================
 constexpr int kWarpCap = 512;
 constexpr int kWarpsPerCta = kPrThreads / 32;
-constexpr int kGrabDefault = 1;      // work items per atomic (DAPB_PR_GRAB overrides): an item keeps a warp busy for tens of
-                                     // microseconds once 48 warps share an SM's gather bandwidth, so the end-of-iteration tail is
-                                     // one GRAB long -- 4 items per grab cost ~50 us of every 290 us iteration at 8 GPUs
+// work items per atomic are chosen per launch (see pagerank_run_impl; DAPB_PR_GRAB overrides): an item keeps a warp busy
+// for tens of microseconds once 48 warps share an SM's gather bandwidth, so the end-of-iteration tail is one GRAB long
 constexpr int kHubDeep = 16;         // measured: 8 -> 16 gathers in flight per lane +5..8 %, 32 no better
 
 template <typename VT>
@@ -442,7 +441,15 @@ int pagerank_run_impl(const DapbPrRunArgs& r, const DapbComm& c, cudaStream_t st
   int grid = per_sm * dapb::sm_count();                 // every CTA must be resident: they wait for each other's flag
   if (r.grid > 0 && r.grid < grid) grid = r.grid;
   const int64_t items = (int64_t)a.n_chunks + a.n_blocks;
-  { static const int g_env = getenv("DAPB_PR_GRAB") ? atoi(getenv("DAPB_PR_GRAB")) : kGrabDefault; a.grab = g_env > 0 ? g_env : 1; }
+  {
+    // items per atomic: one when a warp sees few items per iteration (the tail of the iteration is one grab long), more
+    // when there are hundreds per warp (otherwise ~3e5 same-address atomics per millisecond become the bottleneck:
+    // scale 26 on 8 GPUs measured 1.12 ms with grab 1 against 0.98 ms with grab 4)
+    static const int g_env = getenv("DAPB_PR_GRAB") ? atoi(getenv("DAPB_PR_GRAB")) : 0;
+    const int64_t per_warp = items / ((int64_t)grid * kWarpsPerCta) + 1;
+    const int64_t g_auto = per_warp / 16 < 1 ? 1 : (per_warp / 16 > 8 ? 8 : per_warp / 16);
+    a.grab = g_env > 0 ? g_env : (int)g_auto;
+  }
   const int64_t need = (items + kWarpsPerCta * a.grab - 1) / (kWarpsPerCta * a.grab);
   if (grid > need) grid = need > 0 ? (int)need : 1;
   DAPB_CUDA_CHECK(cudaMemsetAsync(a.sync, 0, 4 * sizeof(uint32_t), st));

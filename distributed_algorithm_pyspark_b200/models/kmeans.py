@@ -154,12 +154,15 @@ class ShardedKMeans:
                 if onehot_gemm:
                     # per-cluster sums as a second cuBLAS GEMM (one-hot^T @ X, fp32 accumulate and output): far faster
                     # on a GPU than index_add_, whose atomics serialise on the k hot rows
-                    oh = torch.nn.functional.one_hot(a, self.k).to(x.dtype)
+                    if getattr(self, "_oh", None) is None or self._oh.shape[0] != x.shape[0]:
+                        self._oh = torch.empty(x.shape[0], self.k, dtype=x.dtype, device=x.device)
+                    oh = self._oh
+                    oh.zero_()
+                    oh.scatter_(1, a[:, None], 1.0)
                     try:
                         sums += torch.mm(oh.T, x, out_dtype=torch.float32) if x.dtype != torch.float32 else oh.T @ x
                     except (TypeError, RuntimeError):
                         sums += (oh.T @ x).float()
-                    del oh
                 else:
                     sums.index_add_(0, a, x.to(self.acc_dtype))
                 cnt += torch.bincount(a, minlength=self.k)
@@ -190,9 +193,16 @@ class ShardedKMeans:
         else:
             cn = (Cc * Cc).sum(1)
             Cm = Cc.to(self.X.dtype)
+            CmT = Cm.T.contiguous()
             for i in range(lo, hi, chunk):
                 x = self.X[i:min(hi, i + chunk)]
-                outs.append((cn[None, :] - 2.0 * (x @ Cm.T).float()).argmin(dim=1))
+                try:        # fp32 output straight from cuBLAS, then two in-place passes and the arg-min
+                    dm = torch.mm(x, CmT, out_dtype=torch.float32) if x.dtype != torch.float32 else x @ CmT
+                except (TypeError, RuntimeError):
+                    dm = (x @ CmT).float()
+                dm.mul_(-2.0).add_(cn[None, :])
+                outs.append(dm.argmin(dim=1))
+                del dm
         return outs[0] if len(outs) == 1 else (torch.cat(outs) if outs else torch.empty(0, dtype=torch.int64, device=self.X.device))
 
     def assign(self) -> torch.Tensor:

@@ -119,7 +119,7 @@ def balanced_vertex_bounds(indeg_all: torch.Tensor, world: int, vertex_cost: Opt
     ids, so equal-size ranges would give rank 0 most of the work and the last rank most of the vertices
     (SURVEY.md 7.3-6).  ``DAPB_PR_VERTEX_COST`` / ``DAPB_PR_HUB_EDGE_COST`` / ``DAPB_PR_PUSH_COST`` override."""
     if vertex_cost is None:
-        vertex_cost = float(os.environ.get("DAPB_PR_VERTEX_COST", 8))
+        vertex_cost = float(os.environ.get("DAPB_PR_VERTEX_COST", 3))      # 8-GPU sweep: 3 beats 8, 1.5 and 1 (profiles/pagerank_n8_sweep_r2.md)
     if hub_edge_cost is None:
         hub_edge_cost = float(os.environ.get("DAPB_PR_HUB_EDGE_COST", 1.0))
     if push_cost is None:
@@ -307,12 +307,15 @@ class ShardedPageRank:
     def _gather(self, loc: torch.Tensor) -> torch.Tensor:
         if self.dist.world == 1:
             return loc.clone()
-        sizes = [(self.g.bounds[r], self.g.bounds[r + 1]) for r in range(self.dist.world)]
+        W = self.dist.world
+        sizes = [(self.g.bounds[r], self.g.bounds[r + 1]) for r in range(W)]
         m = max(b - a for a, b in sizes)
-        pad = torch.zeros(m, dtype=loc.dtype, device=loc.device)
-        pad[:loc.numel()] = loc
-        parts = self.dist.all_gather(pad)
-        return torch.cat([p[:b - a] for p, (a, b) in zip(parts, sizes)])
+        if getattr(self, "_ag_pad", None) is None or self._ag_pad.numel() != m or self._ag_pad.dtype != loc.dtype:
+            self._ag_pad = torch.zeros(m, dtype=loc.dtype, device=loc.device)
+            self._ag_out = torch.empty(W * m, dtype=loc.dtype, device=loc.device)
+        self._ag_pad[:loc.numel()] = loc
+        self.dist.all_gather_into(self._ag_out, self._ag_pad)        # ONE NCCL all-gather of equal (padded) slices
+        return torch.cat([self._ag_out[r * m:r * m + (b - a)] for r, (a, b) in enumerate(sizes)])
 
     def step(self):
         self.run(1)
@@ -404,33 +407,12 @@ class ShardedPageRank:
         return s
 
     def _spmv_baseline(self) -> torch.Tensor:
-        """s = A^T c for the owned rows, baseline arm.  Two straightforward library formulations exist -- cuSPARSE CSR
-        SpMV through ``torch.sparse`` and gather + ``index_add_`` -- and which one wins depends on graph and torch
-        build, so on a GPU both are timed once (second call of each) and the faster one is kept: the baseline is
-        the better of the two.  CPU (gloo tests): gather + ``index_add_``."""
-        if self.g.row_ptr.device.type != "cuda" or self.g.col_idx.numel() < (1 << 16):
-            return self._spmv_gather()
-        if getattr(self, "_spmv_choice", None) is None:
-            times = {}
-            for name, fn in (("gather", self._spmv_gather), ("csr", self._spmv_csr)):
-                try:
-                    fn()
-                    torch.cuda.synchronize()
-                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                    a.record()
-                    fn()
-                    b.record()
-                    torch.cuda.synchronize()
-                    times[name] = a.elapsed_time(b)
-                except Exception:          # noqa: BLE001 -- e.g. sparse CSR unsupported for this dtype
-                    pass
-            # every rank must take the same code path length-wise? no collective inside: a per-rank choice is fine
-            self._spmv_choice = min(times, key=times.get) if times else "gather"
-            if self._spmv_choice == "gather":
-                self._csr = self._csr_hub = None
-            else:
-                self._rows_idx = self._hub_rows_idx = None
-        return self._spmv_csr() if self._spmv_choice == "csr" else self._spmv_gather()
+        """s = A^T c for the owned rows, baseline arm: gather + ``index_add_`` with precomputed row indices.  (cuSPARSE CSR
+        SpMV through ``torch.sparse`` was measured as the alternative -- ``_spmv_csr`` -- and is the slower one here:
+        21 ms against 11 ms per iteration at scale 24 on one B200.)"""
+        if os.environ.get("DAPB_PR_BASELINE_SPMV") == "csr" and self.g.row_ptr.device.type == "cuda":
+            return self._spmv_csr()
+        return self._spmv_gather()
 
     def push_bytes_per_iter(self) -> int:
         """NVLink egress of this rank per iteration: vertices with in- AND out-edges x value size x copies."""

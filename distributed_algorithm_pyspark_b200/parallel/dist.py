@@ -48,6 +48,10 @@ class Dist:
     def all_gather_into(self, out: torch.Tensor, t: torch.Tensor) -> torch.Tensor:
         if self.world == 1:
             out.copy_(t.view_as(out))
+        elif self.device.type != "cuda":        # gloo: list form
+            parts = [torch.empty_like(t) for _ in range(self.world)]
+            dist.all_gather(parts, t.contiguous())
+            out.copy_(torch.cat(parts).view_as(out))
         else:
             dist.all_gather_into_tensor(out, t.contiguous())
         return out
