@@ -57,6 +57,44 @@ def test_standalone_allreduce_world1(lib, heap):
     assert torch.equal(src, dst)
 
 
+def test_grid_collectives_and_stress_world1(lib, heap):
+    """The grid-wide stand-alone collectives, the protocol stress kernel and the fused Monte-Carlo total degenerate to
+    copies at world = 1 but run the same kernels and flag protocol (the multi-rank results are checked in test_multigpu)."""
+    reg = heap.region("test_coll1", 1 << 20, 8)
+    x = torch.randn(4096, device=DEV)
+    for fn in (lib.dapb_allreduce_twoshot_f32, lib.dapb_reduce_scatter_f32):
+        out = torch.zeros_like(x)
+        _native.check(fn(heap.comm_ref(), reg.payload_off, reg.flag_base, reg.next_epoch(), x.data_ptr(), out.data_ptr(),
+                         4096, _native.stream_ptr()))
+        torch.cuda.synchronize()
+        assert torch.equal(out, x)
+    for dt, eb in ((torch.float32, 4), (torch.float64, 8)):
+        xs = torch.randn(1003, device=DEV, dtype=dt)
+        out = torch.zeros_like(xs)
+        _native.check(lib.dapb_allgather(heap.comm_ref(), reg.payload_off, reg.flag_base, reg.next_epoch(), xs.data_ptr(),
+                                         out.data_ptr(), 1003, eb, _native.stream_ptr()))
+        torch.cuda.synchronize()
+        assert torch.equal(out, xs)
+    snd = torch.arange(777, device=DEV, dtype=torch.int64)
+    rcv = torch.zeros_like(snd)
+    _native.check(lib.dapb_alltoall_u64(heap.comm_ref(), reg.payload_off, reg.flag_base, reg.next_epoch(), snd.data_ptr(),
+                                        rcv.data_ptr(), 777, _native.stream_ptr()))
+    fail = torch.zeros(1, dtype=torch.int32, device=DEV)
+    _native.check(lib.dapb_allreduce_stress(heap.comm_ref(), reg.payload_off, reg.flag_base, reg.epoch + 1, 512, 2000, 3,
+                                            fail.data_ptr(), _native.stream_ptr()))
+    reg.epoch += 2000
+    torch.cuda.synchronize()
+    assert torch.equal(rcv, snd) and int(fail.item()) == 0
+    from distributed_algorithm_pyspark_b200.models.monte_carlo import accept_count_np
+    cnt = torch.zeros(1, dtype=torch.int64, device=DEV)
+    tot = torch.zeros(1, dtype=torch.int64, device=DEV)
+    tick = torch.zeros(1, dtype=torch.int32, device=DEV)
+    _native.check(lib.dapb_mc_pi_allreduce(heap.comm_ref(), 7, 100001, 5, cnt.data_ptr(), tot.data_ptr(), tick.data_ptr(),
+                                           reg.payload_off, reg.flag_base, reg.next_epoch(), _native.stream_ptr()))
+    torch.cuda.synchronize()
+    assert int(tot.item()) == int(cnt.item()) == accept_count_np(7, 100001, 5)
+
+
 # ------------------------------------------------------------------------------------------ F1/F2 parity kernel
 @pytest.mark.parametrize("algo", ["ssgd", "gd", "ma", "bmuf", "easgd"])
 def test_lr_parity_kernel_matches_oracle(breast_cancer, dist, algo):
