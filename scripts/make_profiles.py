@@ -21,7 +21,7 @@ KEYS = ["gpu__time_duration.sum", "sm__cycles_elapsed.avg.per_second", "dram__by
         "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "launch__grid_size",
         "launch__block_size", "launch__shared_mem_per_block_dynamic", "smsp__inst_executed.sum"]
 MNEMONICS = ["UTCHMMA", "UTCBAR", "UTMALDG", "UBLKCP", "LDTM", "STTM", "SYNCS", "RED", "ATOM", "HMMA", "LDGSTS", "FMNMX3", "LDG", "STG",
-             "UTCATOMSWS", "ST.E", "LD.E"]
+             "LDGMC", "ACQBULK", "PREEXIT", "ST.E", "LD.E"]
 
 
 def ncu(args):
@@ -81,14 +81,19 @@ def sass_listings():
               "lr_step_kernelI13__nv_bfloat16Li32": "lr_step_kernel_bf16_d1024", "lr_parity_kernel": "lr_parity_kernel",
               "pagerank_step_kernel": "pagerank_step_kernel", "mc_pi_kernel": "mc_pi_kernel", "tc_expand_kernel": "tc_expand_kernel",
               "kmeans_finalize_kernelIfE": "kmeans_finalize_kernel_f32", "lr_tc_kernel": "lr_tc_kernel",
-              "pagerank_warp_kernel": "pagerank_warp_kernel", "pagerank_hub_partial_kernel": "pagerank_hub_partial_kernel",
-              "tc_closure_kernel": "tc_closure_kernel"}
+              "pagerank_run_kernelIfE": "pagerank_run_kernel_f32", "pagerank_run_kernelIdE": "pagerank_run_kernel_f64",
+              "tc_closure_kernel": "tc_closure_kernel", "chol_coop_kernelIfE": "chol_coop_kernel_f32",
+              "eigh_jacobi_kernelIdE": "eigh_jacobi_kernel_f64", "twoshot_kernel": "twoshot_allreduce_kernel",
+              "allgather_kernelIfE": "allgather_kernel_f32"}
     summary = ["# SASS evidence per hot kernel", "",
                "`cuobjdump -sass` of `distributed_algorithm_pyspark_b200/_lib/libdapb200.so` (sm_100a).  `UTCHMMA` = tcgen05.mma, "
                "`LDTM` = tcgen05.ld, `UTMALDG` = TMA tensor load, `UTCBAR` = tcgen05.commit, `SYNCS` = mbarrier ops, "
                "`RED` = no-return atomics (L2 / peer).  Peer-memory pushes are ordinary `ST.E`/`RED` on mapped peer pointers "
-               "followed by `fence.sys` (`MEMBAR.SC.SYS` / `ERRBAR`) and a release store of the epoch flag.", "",
-               "| kernel | instructions | " + " | ".join(MNEMONICS) + " |", "|---|---|" + "---|" * len(MNEMONICS)]
+               "followed by `fence.sys` (`MEMBAR.SC.SYS` / `ERRBAR`) and a release store of the epoch flag.  NVLS: "
+               "`multimem.ld_reduce` = `LDGMC.E.ADD...`, `multimem.st` = `STG.E...STRONG.SYS` on the multicast mapping "
+               "(column `STG.SYS` counts the `STG` with `.STRONG.SYS`: multimem stores and release flag stores).  "
+               "Programmatic dependent launch: `griddepcontrol.wait` = `ACQBULK`, `griddepcontrol.launch_dependents` = `PREEXIT`.", "",
+               "| kernel | instructions | " + " | ".join(MNEMONICS) + " | STG.SYS |", "|---|---|" + "---|" * (len(MNEMONICS) + 1)]
     for f in funcs:
         for key, short in wanted.items():
             if key in f:
@@ -101,7 +106,8 @@ def sass_listings():
                     if t:
                         ops[t.split()[0]] += 1
                 counts = [sum(v for k, v in ops.items() if k.startswith(m)) for m in MNEMONICS]
-                summary.append(f"| {short} | {len(body)} | " + " | ".join(str(c) for c in counts) + " |")
+                stg_sys = sum(v for k, v in ops.items() if k.startswith("STG") and "STRONG.SYS" in k)
+                summary.append(f"| {short} | {len(body)} | " + " | ".join(str(c) for c in counts) + f" | {stg_sys} |")
                 clean = [re.sub(r"\s*/\* 0x[0-9a-f]+ \*/\s*$", "", l) for l in txt.splitlines() if not re.match(r"\s+/\* 0x[0-9a-f]+ \*/\s*$", l)]
                 open(os.path.join(OUT, "sass", short + ".sass"), "w").write("\n".join(clean) + "\n")
     open(os.path.join(OUT, "SASS_SUMMARY.md"), "w").write("\n".join(summary) + "\n")
