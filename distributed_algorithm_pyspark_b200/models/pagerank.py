@@ -121,7 +121,7 @@ def balanced_vertex_bounds(indeg_all: torch.Tensor, world: int, vertex_cost: Opt
     if vertex_cost is None:
         vertex_cost = float(os.environ.get("DAPB_PR_VERTEX_COST", 3))      # 8-GPU sweep: 3 beats 8, 1.5 and 1 (profiles/pagerank_n8_sweep_r2.md)
     if hub_edge_cost is None:
-        hub_edge_cost = float(os.environ.get("DAPB_PR_HUB_EDGE_COST", 1.0))
+        hub_edge_cost = float(os.environ.get("DAPB_PR_HUB_EDGE_COST", 0.65))    # hub non-zeros stream through the chunk path: cheaper per edge (8-GPU sweep)
     if push_cost is None:
         push_cost = float(os.environ.get("DAPB_PR_PUSH_COST", 2.0))
     V = indeg_all.numel()
