@@ -287,6 +287,15 @@ __global__ void __launch_bounds__(kPrThreads, sizeof(VT) == 4 ? 6 : 4) pagerank_
           if (lane == 0) {
             const int hi = a.chunk_row[item];
             const int ch0 = a.hub_chunk_ptr[hi], ch1 = a.hub_chunk_ptr[hi + 1];
+            if (ch1 - ch0 == 1) {
+              // the common case (half a million rows of 65..2048 in-edges at scale 24): the row IS the chunk -- no
+              // partial, no fence, no counter.  (ncu showed the two __threadfence of the general path, executed once per
+              // chunk, as the top stall of the kernel: MEMBAR.SC.GPU + CCTL.IVALL, 16 % stall_membar; with peers they
+              // also wait for the warp's outstanding NVLink stores.)
+              const int32_t row = a.hub_rows[hi];
+              pr_emit(a, c, next_off, row, s, a.inv_outdeg[row]);
+              continue;
+            }
             a.chunk_partial[item] = s;
             __threadfence();
             const uint32_t done = atomicAdd(a.row_done + hi, 1u);
