@@ -744,7 +744,7 @@ extern "C" int dapb_lr_step(const DapbLrStepArgs* args, const DapbComm* comm, vo
 //               tcgen05.ld of the gradient accumulators -> this CTA's partial row
 //   warps 8-23  two loader groups of 8 warps working on alternating slabs (64 KB in flight per SM)
 // The partial rows go through the same deterministic grid reduction + in-kernel peer all-reduce + optimiser
-// update (lr_finalize) as the CUDA-core kernel.
+// update (lr_grid_finish) as the CUDA-core kernel.
 namespace {
 
 constexpr int kTcThreads = 768;

@@ -118,7 +118,7 @@ DAPB_API uint64_t dapb_lr_parity_payload_bytes(int32_t P_global, int32_t D);
 
 /* One optimiser step at benchmark scale, ONE launch: Bernoulli row sample (Philox or explicit
  * mask) -> forward z = Xw -> r = sigmoid(z) - y -> backward g = X^T r -> deterministic grid
- * reduction -> [last CTA] in-kernel all-reduce over NVLink peers -> optimiser update. */
+ * reduction -> [last 8 CTAs, one column slice each] in-kernel all-reduce over NVLink peers -> optimiser update. */
 enum { DAPB_LR_FIN_GRAD_ONLY = 0,   /* g_out[D], cnt_out only                                  */
        DAPB_LR_FIN_SSGD = 1,        /* all-reduce(g,cnt); w -= eta*(g/cnt + lam*reg(w))  (or sum: GD) */
        DAPB_LR_FIN_LOCAL = 2,       /* w_p -= eta*g/cnt + alpha*(w_p - centre)                 */
