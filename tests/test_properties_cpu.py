@@ -112,3 +112,50 @@ def test_vertex_bounds_cover_the_range_and_balance_cost(indeg, world, vertex_cos
     total, biggest = float(cost.sum()), float(cost.max())
     for r in range(world):
         assert float(cost[b[r]:b[r + 1]].sum()) <= total / world + biggest + 1e-6
+
+
+# ------------------------------------------------------------------------------------------ PageRank host-side layout
+@settings(**common)
+@given(st.integers(0, 2 ** 31 - 1), st.integers(2, 8), st.integers(1, 40), st.integers(4, 64))
+def test_hub_split_and_partition_invariants(seed, world, threshold, chunk):
+    """split_hub_rows: every non-zero lands exactly once in the main CSR or in a hub chunk, chunks tile their rows in order
+    and know their row; balanced_vertex_bounds: contiguous cover of [0, V), modelled cost of every rank within one vertex
+    of the mean."""
+    import torch
+    from distributed_algorithm_pyspark_b200.models.pagerank import balanced_vertex_bounds, split_hub_rows
+    g = torch.Generator().manual_seed(seed)
+    V = 200
+    lens = (torch.rand(V, generator=g) ** 4 * 120).long()
+    lens[torch.rand(V, generator=g) < 0.3] = 0
+    row_ptr = torch.zeros(V + 1, dtype=torch.int64)
+    row_ptr[1:] = torch.cumsum(lens, 0)
+    col = torch.randint(0, V, (int(row_ptr[-1]),), generator=g).to(torch.int32)
+    rp, main_col, hub = split_hub_rows(row_ptr, col, threshold, chunk)
+    main_lens = rp[1:] - rp[:-1]
+    is_hub = lens > threshold
+    assert torch.equal(main_lens[~is_hub], lens[~is_hub]) and int(main_lens[is_hub].sum()) == 0
+    assert torch.equal(hub.rows.long(), torch.nonzero(is_hub).flatten())
+    assert main_col.numel() + hub.col.numel() == col.numel()
+    if hub.rows.numel():
+        assert torch.equal(hub.ptr[1:] - hub.ptr[:-1], lens[is_hub])
+        # chunks: consecutive, at most `chunk` long, each inside its own row, chunk_row consistent with chunk_ptr
+        for i in range(hub.rows.numel()):
+            c0, c1 = int(hub.chunk_ptr[i]), int(hub.chunk_ptr[i + 1])
+            assert c1 > c0 and int(hub.chunk_start[c0]) == int(hub.ptr[i]) and int(hub.chunk_end[c1 - 1]) == int(hub.ptr[i + 1])
+            for ch in range(c0, c1):
+                assert int(hub.chunk_row[ch]) == i and 0 < int(hub.chunk_end[ch] - hub.chunk_start[ch]) <= chunk
+                if ch > c0:
+                    assert int(hub.chunk_start[ch]) == int(hub.chunk_end[ch - 1])
+        # the hub non-zeros are the original ones, row after row
+        want = torch.cat([col[int(row_ptr[r]):int(row_ptr[r + 1])] for r in hub.rows.tolist()])
+        assert torch.equal(hub.col, want)
+    outdeg = torch.bincount(col.long(), minlength=V)
+    b = balanced_vertex_bounds(lens, world, vertex_cost=3.0, hub_threshold=threshold, hub_edge_cost=0.65,
+                               outdeg_all=outdeg, push_cost=2.0)
+    assert b[0] == 0 and b[-1] == V and all(b[i] <= b[i + 1] for i in range(world))
+    deg = lens.double()
+    per_v = torch.where(lens > threshold, deg * 0.65, deg) + 3.0 * (lens > 0) + 1 + 2.0 * ((lens > 0) & (outdeg > 0))
+    total, vmax = float(per_v.sum()), float(per_v.max())
+    for r in range(world):
+        share = float(per_v[b[r]:b[r + 1]].sum())
+        assert share <= total / world + vmax + 1e-9
