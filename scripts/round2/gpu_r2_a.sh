@@ -1,6 +1,6 @@
 #!/bin/bash
 # round-2 call A (2 GPUs): NVLS probe + new collectives + persistent PageRank
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=index,name --format=csv > gpurun_out/a_gpus.txt 2>&1
 timeout 900 python -m pytest tests/test_multigpu.py -x -q > gpurun_out/a_multigpu.log 2>&1; echo "multigpu rc=$?" 

@@ -1,6 +1,6 @@
 #!/bin/bash
 # round-2 call B (2 GPUs): full GPU test-suite + SSGD headline with the slice-parallel finish (PDL on / off)
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q --timeout 900 > gpurun_out/b_pytest.log 2>&1; echo "pytest rc=$?"
 tail -8 gpurun_out/b_pytest.log

@@ -1,6 +1,6 @@
 #!/bin/bash
 # round-2 call C (2 GPUs): tests + smoke + reworked bench (baselines, checks, full configs)
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q --timeout 900 > gpurun_out/c_pytest.log 2>&1; echo "pytest rc=$?"
 tail -8 gpurun_out/c_pytest.log

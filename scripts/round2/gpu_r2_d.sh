@@ -1,6 +1,6 @@
 #!/bin/bash
 # round-2 call D (2 GPUs): SYRK Gram + cooperative Cholesky + Jacobi eigen-solver; PageRank at 6 CTAs/SM
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q --timeout 900 > gpurun_out/d_pytest.log 2>&1; echo "pytest rc=$?"
 tail -15 gpurun_out/d_pytest.log

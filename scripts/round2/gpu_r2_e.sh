@@ -1,5 +1,5 @@
 #!/bin/bash
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests/test_gpu_kernels.py tests/test_gpu_tc_kernels.py -x -q --timeout 600 -k "eigh or cholesky or gram or kmeans or pagerank" > gpurun_out/e_pytest.log 2>&1; echo "pytest rc=$?"
 tail -6 gpurun_out/e_pytest.log

@@ -1,5 +1,5 @@
 #!/bin/bash
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests/test_gpu_tc_kernels.py tests/test_gpu_kernels.py -x -q --timeout 600 -k "eigh or cholesky or gram or als" > gpurun_out/f2_pytest.log 2>&1; echo "pytest rc=$?"
 tail -4 gpurun_out/f2_pytest.log

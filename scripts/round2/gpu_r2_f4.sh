@@ -1,5 +1,5 @@
 #!/bin/bash
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_gpu_kernels.py tests/test_gpu_tc_kernels.py -x -q --timeout 600 -k "cholesky or als or gram" > gpurun_out/f4_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/f4_pytest.log
 timeout 120 python scripts/chol_eigh_probe.py 2>/dev/null | tail -1 | tee gpurun_out/f4_chol_eigh.json

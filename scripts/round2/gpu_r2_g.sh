@@ -1,6 +1,6 @@
 #!/bin/bash
 # round-2 call G (8 GPUs): multi-GPU tests at 4 ranks, PageRank partition sweep at scale 24 / 26
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests/test_multigpu.py -x -q --timeout 800 > gpurun_out/g_multigpu.log 2>&1; echo "multigpu rc=$?"; tail -3 gpurun_out/g_multigpu.log
 export DAPB_BENCH_SKIP_PR24=1

@@ -1,6 +1,6 @@
 #!/bin/bash
 # round-2 call H (2 GPUs): PageRank tail experiments (grab size, block size) on small per-rank work + fp32 k-means path
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 export DAPB_BENCH_SKIP_PR24=1
 timeout 600 python -m pytest tests/test_gpu_kernels.py -x -q --timeout 600 -k "kmeans or pagerank" > gpurun_out/h_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/h_pytest.log

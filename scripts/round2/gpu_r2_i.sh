@@ -1,6 +1,6 @@
 #!/bin/bash
 # round-2 call I (8 GPUs): full bench at N = 8 (+ headline-only N = 1 on the same box)
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 ( time timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29670 \
   bench.py --gpus 8 --steps 20 --warmup 5 > gpurun_out/i_bench_n8.json 2> gpurun_out/i_bench_n8.err ) 2> gpurun_out/i_bench_n8.time; echo "bench n=8 rc=$?"; tail -3 gpurun_out/i_bench_n8.time

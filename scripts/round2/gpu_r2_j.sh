@@ -1,6 +1,6 @@
 #!/bin/bash
 # round-2 call J (1 GPU): full GPU test-suite, smoke, full bench at N = 1, launch list under ncu
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q --timeout 900 > gpurun_out/j_pytest.log 2>&1; echo "pytest rc=$?"
 tail -6 gpurun_out/j_pytest.log

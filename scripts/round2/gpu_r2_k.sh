@@ -1,6 +1,6 @@
 #!/bin/bash
 # round-2 call K (8 GPUs): PageRank partition fine-tuning (hub edge cost, grab)
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 export DAPB_BENCH_SKIP_PR24=1
 run() {  # scale hub_edge_cost grab tag

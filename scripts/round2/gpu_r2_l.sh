@@ -1,6 +1,6 @@
 #!/bin/bash
 # round-2 call L (1 GPU): ncu --set full of the round-2 kernels at benchmark shape (each after the plain command exited 0)
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 export DAPB_BENCH_SKIP_PR24=1
 run() {  # name regex skip cmd...

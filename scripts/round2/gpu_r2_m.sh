@@ -1,6 +1,6 @@
 #!/bin/bash
 # round-2 call M (2 GPUs): PageRank after the fence fix (tests, 1- and 2-GPU timing), k-means ncu capture
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 export DAPB_BENCH_SKIP_PR24=1
 timeout 900 python -m pytest tests/test_gpu_kernels.py tests/test_multigpu.py -x -q --timeout 800 -k "pagerank or multi_gpu or resume or entry" > gpurun_out/m_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/m_pytest.log

@@ -1,6 +1,6 @@
 #!/bin/bash
 # round-2 call N (8 GPUs): PageRank after the fence fix -- hub edge cost re-tuned
-cd "$(dirname "$0")/.."
+cd "$(dirname "$0")/../.."
 mkdir -p gpurun_out
 export DAPB_BENCH_SKIP_PR24=1
 run() {  # scale hub_edge_cost vertex_cost tag
