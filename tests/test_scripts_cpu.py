@@ -43,3 +43,17 @@ def test_other_scripts_stdout(tmp_path):
     assert len(out) == 5 and out[0] == "iterations: 0, rmse: 0.224488" and out[4].startswith("iterations: 4, rmse: 0.0314")
     assert re.fullmatch(r"Pi is roughly 3\.1\d{5}", _run("randomized_algorithm/monte_carlo.py", "--backend", "torch", tmp=tmp_path).strip())
     assert (tmp_path / "matrix_decomposition_result.npz").exists() and (tmp_path / "kmeans_clusters_display.npy").exists()
+
+
+def test_bench_reference_arm_contract():
+    """`bench.py --impl reference` must print one JSON line with impl = reference and exit 0 (the reference cannot be
+    installed offline: ten PySpark scripts, no pyspark / JVM in the image)."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "3",
+                          "--warmup", "3"], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr[-500:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["n_gpus"] == 2 and "unavailable" in line
